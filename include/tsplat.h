@@ -1,0 +1,171 @@
+/*
+ * tsplat.h — C-ABI of libtsplat.so, the sm_100a differentiable Gaussian-splat rasterizer.
+ *
+ * This is the drop-in boundary for the render path of TranSplat
+ * (/root/reference/src/model/decoder/cuda_splatting.py).  Every entry point below replaces
+ * one binding of the external extension `diff_gaussian_rasterization`
+ * (requirements.txt:17) that the reference reaches through
+ *   - cuda_splatting.py:6-9      import GaussianRasterizationSettings, GaussianRasterizer
+ *   - cuda_splatting.py:108-133  settings construction + rasterizer(...) call (render_cuda)
+ *   - cuda_splatting.py:201-226  same call pattern (render_cuda_orthographic)
+ *   - cuda_splatting.py:323-348  same call pattern (render_cuda_with_stats; reads radii)
+ *   - cuda_splatting.py:404      render_depth_cuda -> a second render_cuda pass
+ * and, one level up, the batched decoder call
+ *   - decoder_splatting_cuda.py:41-97  DecoderSplattingCUDA.forward / render_depth.
+ *
+ * Conventions
+ *   - plain C, no torch types; every pointer is a DEVICE pointer owned by the caller unless the
+ *     parameter name ends in _host;
+ *   - the library never allocates or frees device memory, never synchronises the device and
+ *     only enqueues work on the stream it is given;
+ *   - return value 0 = ok, otherwise a TSPLAT_E* code; tsplat_last_error() gives the text
+ *     (thread-local);
+ *   - the size of the tile/Gaussian pair list ("num_rendered", D) is not known on the host:
+ *     the caller supplies a capacity d_cap; if D > d_cap the status block's `overflow` flag is
+ *     set, pairs beyond the capacity are dropped, and the caller retries with a larger
+ *     workspace (tsplat_status_read tells it how large).
+ */
+#ifndef TSPLAT_H_
+#define TSPLAT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TSPLAT_VERSION 100
+
+/* error codes */
+#define TSPLAT_OK 0
+#define TSPLAT_EINVAL 1    /* bad shape / null pointer / unsupported option          */
+#define TSPLAT_ENOSPC 2    /* workspace too small for (problem, d_cap)                */
+#define TSPLAT_ECUDA 3     /* a CUDA runtime call or launch failed                    */
+
+/* tile geometry is part of the parity contract (tiles_touched, keys, ranges depend on it) */
+#define TSPLAT_TILE 16
+
+/* layouts of the spherical-harmonics tensor */
+#define TSPLAT_SH_GM3 0 /* [G, M, 3]  what the reference passes as `shs` (cuda_splatting.py:84,129) */
+#define TSPLAT_SH_G3M 1 /* [G, 3, M]  Gaussians.harmonics as the encoder emits it (types.py:11)     */
+/* layouts of the covariance tensor */
+#define TSPLAT_COV_TRIU6 0 /* [G, 6] xx,xy,xz,yy,yz,zz (cuda_splatting.py:124,132)  */
+#define TSPLAT_COV_FULL9 1 /* [G, 3, 3] Gaussians.covariances (types.py:10)          */
+
+/* fused depth channel (render_depth_cuda, cuda_splatting.py:375-417) */
+#define TSPLAT_DEPTH_NONE 0
+#define TSPLAT_DEPTH_DEPTH 1
+#define TSPLAT_DEPTH_DISPARITY 2
+#define TSPLAT_DEPTH_RELATIVE_DISPARITY 3
+#define TSPLAT_DEPTH_LOG 4
+
+/*
+ * One camera = 64 floats (256 B).  Matrices use the reference's flat convention: element
+ * (row r, col c) of the conventional column-vector matrix is m[4*c + r]
+ * (cuda_splatting.py:94-96 passes transposes).
+ */
+typedef struct TsplatCamera {
+  float view[16];     /* GaussianRasterizationSettings.viewmatrix   (cuda_splatting.py:95,115)  */
+  float proj[16];     /* GaussianRasterizationSettings.projmatrix   (cuda_splatting.py:96,116)  */
+  float campos[3];    /* GaussianRasterizationSettings.campos       (cuda_splatting.py:118)     */
+  float tanfovx;      /* (cuda_splatting.py:111) */
+  float tanfovy;      /* (cuda_splatting.py:112) */
+  float bg[3];        /* GaussianRasterizationSettings.bg           (cuda_splatting.py:113)     */
+  float mean_scale;   /* s = 1/near applied to means (cuda_splatting.py:74-77); 1 at level 1   */
+  float cov_scale;    /* s*s applied to covariances (cuda_splatting.py:76); 1 at level 1       */
+  float depth_row[4]; /* row 2 of inverse(extrinsics), unscaled (cuda_splatting.py:388-391)     */
+  float near_plane;   /* unscaled near (relative_disparity / log, cuda_splatting.py:395-400)    */
+  float far_plane;    /* unscaled far                                                           */
+  float reserved[16];
+} TsplatCamera;
+
+/*
+ * One call = B scenes x V target views per scene, all scenes with G Gaussians and all views HxW.
+ * Level 1 (GaussianRasterizer.forward) uses B = V = 1, SH_GM3, COV_TRIU6, DEPTH_NONE.
+ * Level 2 (DecoderSplattingCUDA.forward) passes the encoder's tensors untouched.
+ */
+typedef struct TsplatProblem {
+  int32_t B;          /* scenes                                                                  */
+  int32_t G;          /* Gaussians per scene                                                     */
+  int32_t V;          /* views per scene                                                         */
+  int32_t H, W;       /* image size (settings.image_height/width, cuda_splatting.py:109-110)     */
+  int32_t sh_degree;  /* active degree 0..4 (settings.sh_degree, cuda_splatting.py:117)          */
+  int32_t sh_coeffs;  /* M coefficients stored per channel; 0 => `sh` holds colors_precomp [G,3] */
+  int32_t sh_layout;  /* TSPLAT_SH_*                                                             */
+  int32_t cov_layout; /* TSPLAT_COV_*                                                            */
+  int32_t depth_mode; /* TSPLAT_DEPTH_*; != NONE adds the fused 4th (depth) channel              */
+  int32_t sh_l4;      /* 1: evaluate the l=4 band when sh_degree>=4, 0: ignore it   */
+  int32_t reserved0;
+  const float* means;   /* [B, G, 3]                                                             */
+  const float* cov;     /* [B, G, 6] or [B, G, 3, 3]                                             */
+  const float* sh;      /* [B, G, M, 3] / [B, G, 3, M] / colors_precomp [B, G, 3]                */
+  const float* opacity; /* [B, G]                                                                */
+  const TsplatCamera* cams; /* [B*V]                                                             */
+} TsplatProblem;
+
+/* Byte offsets of the inspectable workspace sections (all 256-B aligned).  N = B*V views. */
+typedef struct TsplatLayout {
+  uint64_t total_bytes;
+  uint64_t status;        /* TsplatStatus                                                         */
+  uint64_t depths;        /* float  [N, G]   camera-space z (the low key word)                    */
+  uint64_t radii;         /* int32  [N, G]                                                        */
+  uint64_t xy;            /* float2 [N, G]   pixel-space centre                                   */
+  uint64_t conic_opacity; /* float4 [N, G]                                                        */
+  uint64_t rgbd;          /* float4 [N, G]   r, g, b, depth feature                               */
+  uint64_t tiles_touched; /* uint32 [N, G]                                                        */
+  uint64_t clamped;       /* uint8  [N, G]   bit c set => channel c was clamped at 0              */
+  uint64_t keys;          /* uint64 [d_cap]  sorted: ((view*T + tile) << 32) | depth bits         */
+  uint64_t vals;          /* uint32 [d_cap]  sorted Gaussian index within its scene               */
+  uint64_t ranges;        /* uint2  [N*T]    [first, last) per (view, tile)                       */
+  uint64_t final_T;       /* float  [N, H, W]                                                     */
+  uint64_t n_contrib;     /* uint32 [N, H, W]                                                     */
+  uint64_t grad_acc;      /* float  [N, G, 12] screen-space gradient accumulators (backward)      */
+  int32_t tiles_x, tiles_y; /* grid                                                               */
+  int32_t sort_bits;      /* number of key bits the sort covers                                   */
+  int32_t sort_passes;
+} TsplatLayout;
+
+/* Device-side status block (first bytes of the workspace). */
+typedef struct TsplatStatus {
+  uint64_t num_rendered; /* D over all views of the call (may exceed d_cap when overflow != 0)    */
+  uint32_t overflow;     /* 1 if D > d_cap                                                        */
+  uint32_t reserved;
+} TsplatStatus;
+
+int tsplat_version(void);
+const char* tsplat_last_error(void);
+
+/* Replaces the resize lambdas + GeometryState/BinningState/ImageState::fromChunk carving of the
+ * extension: one caller-owned workspace, size known up front. */
+int tsplat_workspace_layout(const TsplatProblem* p, uint64_t d_cap, TsplatLayout* out);
+
+/* Replaces _C.rasterize_gaussians.
+ *   out_color [B*V, 3, H, W]; out_depth [B*V, H, W] or NULL (required iff depth_mode != NONE);
+ *   out_radii [B*V, G] int32 or NULL. */
+int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes,
+                   uint64_t d_cap, float* out_color, float* out_depth, int32_t* out_radii,
+                   void* cuda_stream);
+
+/* Replaces _C.rasterize_gaussians_backward.  Must follow tsplat_forward on
+ * the same (problem, workspace).  Gradients are summed over the V views of each scene and
+ * WRITTEN (not accumulated):
+ *   dL_dmeans [B,G,3]; dL_dcov [B,G,6] or [B,G,3,3] (upper triangle filled, lower zero);
+ *   dL_dsh same layout as p->sh; dL_dopacity [B,G];
+ *   dL_dmeans2D [B*V, G, 3] or NULL (gradient of the dummy screen-space tensor, level 1). */
+int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes,
+                    uint64_t d_cap, const float* dL_dcolor, const float* dL_ddepth,
+                    float* dL_dmeans, float* dL_dcov, float* dL_dsh, float* dL_dopacity,
+                    float* dL_dmeans2D, void* cuda_stream);
+
+/* Replaces _C.mark_visible (GaussianRasterizer.markVisible).  present [G] uint8. */
+int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix,
+                        const float* projmatrix, uint8_t* present, void* cuda_stream);
+
+/* Copies the status block to pinned/pageable host memory asynchronously on the stream. */
+int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSPLAT_H_ */
