@@ -1,0 +1,126 @@
+"""Shared helpers of the parity tests: run the CPU oracle and the CUDA library on the same inputs
+and compare stage by stage.  The oracle is the checker; the CUDA path is the thing checked."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+import oracle
+from transplat_b200.rasterize import RenderConfig, backward_raw, forward_raw, inspect_workspace
+
+COLOR_ATOL = 1e-5   # north_star: rendered colour/depth within 1e-5 abs
+GRAD_RTOL = 1e-4    # north_star: Gaussian gradients within 1e-4 relative (to the tensor's max-abs)
+
+
+def oracle_batch(means, cov, sh, opacity, cams, cfg: RenderConfig, dL_dcolor=None, dL_ddepth=None):
+    """means [B,G,3] ... numpy/torch CPU; cams [B*V,64].  Returns (list of ViewState, list of GradAccum|None)."""
+    to_np = lambda t: t.detach().cpu().numpy() if torch.is_tensor(t) else np.asarray(t)
+    means, cov, sh, opacity, cams = map(to_np, (means, cov, sh, opacity, cams))
+    B = means.shape[0]
+    states, accs = [], []
+    for b in range(B):
+        scene = oracle.Scene(means[b], cov[b], sh[b], opacity[b], cfg.sh_degree, cfg.sh_layout,
+                             cfg.cov_layout, cfg.sh_l4)
+        acc = oracle.GradAccum(scene) if dL_dcolor is not None else None
+        for v in range(cfg.V):
+            n = b * cfg.V + v
+            st = oracle.forward(scene, cams[n], cfg.H, cfg.W, depth_mode=cfg.depth_mode)
+            states.append(st)
+            if acc is not None:
+                oracle.backward(scene, cams[n], st, to_np(dL_dcolor)[n],
+                                to_np(dL_ddepth)[n] if cfg.depth_mode else None, acc=acc,
+                                depth_mode=cfg.depth_mode)
+                st.extra["mean2d"] = acc.mean2d
+                st.extra["screen"] = acc.screen
+        accs.append(acc)
+    return states, accs
+
+
+def compare_forward(ins: dict, color, depth, states, cfg: RenderConfig) -> dict:
+    """Bit-exact checks on integer/bit quantities, tolerance checks on colour/depth."""
+    T = ins["T"]
+    rep = {"views": len(states)}
+    cpu = {k: (v.cpu().numpy() if torch.is_tensor(v) else v) for k, v in ins.items()}
+    color, depth = color.cpu().numpy(), (depth.cpu().numpy() if depth is not None else None)
+    D_total, off = 0, 0
+    rep.update(radii_mismatch=0, depth_bits_mismatch=0, tiles_touched_mismatch=0, xy_bits_mismatch=0,
+               clamped_mismatch=0, keys_mismatch=0, vals_mismatch=0, ranges_mismatch=0, n_contrib_mismatch=0,
+               conic_max_abs=0.0, rgbd_max_abs=0.0, color_max_abs=0.0, depth_max_abs=0.0, final_T_max_abs=0.0)
+    for n, st in enumerate(states):
+        rep["radii_mismatch"] += int((cpu["radii"][n] != st.radii).sum())
+        rep["depth_bits_mismatch"] += int((cpu["depths"][n].view(np.uint32) != st.depths.view(np.uint32)).sum())
+        rep["tiles_touched_mismatch"] += int((cpu["tiles_touched"][n].astype(np.uint32) != st.tiles_touched).sum())
+        rep["xy_bits_mismatch"] += int((cpu["xy"][n].view(np.uint32) != st.xy.view(np.uint32)).sum())
+        rep["clamped_mismatch"] += int((cpu["clamped"][n] != st.clamped).sum())
+        rep["conic_max_abs"] = max(rep["conic_max_abs"], float(np.abs(cpu["conic_opacity"][n] - st.conic_opacity).max(initial=0)))
+        rep["rgbd_max_abs"] = max(rep["rgbd_max_abs"], float(np.abs(cpu["rgbd"][n] - st.rgbd).max(initial=0)))
+        D = st.num_rendered
+        gk = cpu["keys"][off:off + D].view(np.uint64)
+        gv = cpu["vals"][off:off + D].view(np.uint32)
+        if gk.shape[0] != D:
+            rep["keys_mismatch"] += D
+        else:
+            ok = st.keys + (np.uint64(n * T) << np.uint64(32))
+            rep["keys_mismatch"] += int((gk != ok).sum())
+            rep["vals_mismatch"] += int((gv != st.vals).sum())
+        r = cpu["ranges"][n].astype(np.int64)
+        o = st.ranges.astype(np.int64).copy()
+        nonempty = o[:, 1] > o[:, 0]
+        o[nonempty] += off
+        rep["ranges_mismatch"] += int((r[nonempty] != o[nonempty]).sum()) + int(
+            ((r[~nonempty, 1] - r[~nonempty, 0]) != 0).sum())
+        rep["n_contrib_mismatch"] += int((cpu["n_contrib"][n].astype(np.uint32) != st.n_contrib).sum())
+        rep["final_T_max_abs"] = max(rep["final_T_max_abs"], float(np.abs(cpu["final_T"][n] - st.final_T).max()))
+        rep["color_max_abs"] = max(rep["color_max_abs"], float(np.abs(color[n] - st.color).max()))
+        if depth is not None:
+            rep["depth_max_abs"] = max(rep["depth_max_abs"], float(np.abs(depth[n] - st.depth).max()))
+        off += D
+        D_total += D
+    rep["num_rendered_gpu"] = cpu["num_rendered"]
+    rep["num_rendered_oracle"] = D_total
+    return rep
+
+
+def rel_err(a: np.ndarray, ref: np.ndarray) -> float:
+    m = float(np.abs(ref).max())
+    return float(np.abs(a - ref).max()) / m if m > 0 else float(np.abs(a).max())
+
+
+def compare_backward(grads, accs) -> dict:
+    g_means, g_cov, g_sh, g_op = (g.cpu().numpy().astype(np.float64) for g in grads[:4])
+    rep = {}
+    for name, g, pick in (("means", g_means, lambda a: a.means), ("cov", g_cov, lambda a: a.cov),
+                          ("sh", g_sh, lambda a: a.sh), ("opacity", g_op, lambda a: a.opacity)):
+        ref = np.stack([pick(a) for a in accs])
+        rep[name + "_rel"] = rel_err(g, ref)
+        rep[name + "_maxabs_ref"] = float(np.abs(ref).max())
+    return rep
+
+
+def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=True, seed=7):
+    """Everything on the same seeded inputs.  Returns (forward report, backward report|None)."""
+    dev = torch.device("cuda:0")
+    cfg.check = "sync"
+    gm, gc, gs, go, gcam = (t.to(dev) for t in (means, cov, sh, opacity, cams))
+    color, depth, radii, state = forward_raw(cfg, gm, gc, gs, go, gcam)
+    ins = inspect_workspace(state)
+    N = cams.shape[0]
+    g = torch.Generator().manual_seed(seed)
+    dLc = torch.randn(N, 3, cfg.H, cfg.W, generator=g)
+    dLd = torch.randn(N, cfg.H, cfg.W, generator=g)
+    states, accs = oracle_batch(means, cov, sh, opacity, cams, cfg, dLc if with_backward else None, dLd)
+    fwd = compare_forward(ins, color, depth, states, cfg)
+    if radii is not None:
+        fwd["out_radii_mismatch"] = int(sum((radii[n].cpu().numpy() != st.radii).sum() for n, st in enumerate(states)))
+    bwd = None
+    if with_backward:
+        grads = backward_raw(cfg, state, dLc.to(dev), dLd.to(dev) if cfg.depth_mode else None)
+        torch.cuda.synchronize()
+        bwd = compare_backward(grads, accs)
+        if grads[4] is not None:
+            ref2d = np.stack([st.extra["mean2d"] for st in states])
+            bwd["mean2d_rel"] = rel_err(grads[4].cpu().numpy().astype(np.float64), ref2d)
+        acc_gpu = inspect_workspace(state)["grad_acc"].cpu().numpy().astype(np.float64)
+        scr = np.stack([st.extra["screen"] for st in states])
+        bwd["screen_rel"] = max(rel_err(acc_gpu[..., k], scr[..., k]) for k in range(10 if cfg.depth_mode else 9))
+    return fwd, bwd

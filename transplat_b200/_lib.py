@@ -1,0 +1,77 @@
+"""ctypes binding of ``libtsplat.so`` (include/tsplat.h).  There is no CPU fallback: if the
+library is missing or cannot be loaded every entry point raises."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libtsplat.so")
+CSRC = os.path.join(_HERE, "csrc")
+
+TSPLAT_OK, TSPLAT_EINVAL, TSPLAT_ENOSPC, TSPLAT_ECUDA = 0, 1, 2, 3
+SH_GM3, SH_G3M = 0, 1
+COV_TRIU6, COV_FULL9 = 0, 1
+DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
+
+EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
+           "tsplat_backward", "tsplat_mark_visible", "tsplat_status_read")
+
+
+class TsplatProblem(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in (
+        "B", "G", "V", "H", "W", "sh_degree", "sh_coeffs", "sh_layout", "cov_layout", "depth_mode",
+        "sh_l4", "reserved0")] + [(n, C.c_void_p) for n in ("means", "cov", "sh", "opacity", "cams")]
+
+
+class TsplatLayout(C.Structure):
+    _fields_ = [(n, C.c_uint64) for n in (
+        "total_bytes", "status", "depths", "radii", "xy", "conic_opacity", "rgbd", "tiles_touched",
+        "clamped", "keys", "vals", "ranges", "final_T", "n_contrib", "grad_acc")] + [
+        (n, C.c_int32) for n in ("tiles_x", "tiles_y", "sort_bits", "sort_passes")]
+
+
+class TsplatStatus(C.Structure):
+    _fields_ = [("num_rendered", C.c_uint64), ("overflow", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+def build(verbose: bool = False) -> str:
+    """Compile every kernel for sm_100a with nvcc (cross-compiles without a GPU)."""
+    out = subprocess.run(["make", "-C", CSRC, "-j8"], capture_output=True, text=True)
+    if out.returncode != 0:
+        raise RuntimeError("building libtsplat.so failed:\n" + out.stdout + out.stderr)
+    if verbose:
+        print(out.stdout)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(there is no CPU fallback for the render path)")
+        L = C.CDLL(LIB_PATH)
+        L.tsplat_version.restype = C.c_int
+        L.tsplat_last_error.restype = C.c_char_p
+        L.tsplat_workspace_layout.argtypes = [C.POINTER(TsplatProblem), C.c_uint64, C.POINTER(TsplatLayout)]
+        L.tsplat_forward.argtypes = [C.POINTER(TsplatProblem), C.c_void_p, C.c_uint64, C.c_uint64,
+                                     C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_backward.argtypes = [C.POINTER(TsplatProblem), C.c_void_p, C.c_uint64, C.c_uint64,
+                                      C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_status_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != TSPLAT_OK:
+        msg = lib().tsplat_last_error().decode()
+        raise RuntimeError(f"{what} failed (code {rc}): {msg}")

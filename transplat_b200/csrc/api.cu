@@ -1,0 +1,232 @@
+// api.cu — the C-ABI of libtsplat.so (include/tsplat.h): workspace carving and stage orchestration.
+// Replaces rasterize_points.cu + CudaRasterizer::Rasterizer::{forward,backward} of the reference's
+// external extension.  Nothing here allocates device memory or synchronises.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace tsplat {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+static int bits_for(uint64_t n) {  // smallest b with n <= 2^b
+  int b = 0;
+  while (((uint64_t)1 << b) < n) b++;
+  return b;
+}
+
+static int validate(const TsplatProblem* p, uint64_t d_cap) {
+  if (!p) { set_error("problem is NULL"); return TSPLAT_EINVAL; }
+  if (p->B < 1 || p->V < 1 || p->G < 0 || p->H < 1 || p->W < 1) {
+    set_error("bad sizes B=%d G=%d V=%d H=%d W=%d", p->B, p->G, p->V, p->H, p->W);
+    return TSPLAT_EINVAL;
+  }
+  if (p->sh_degree < 0 || p->sh_degree > 4) { set_error("sh_degree %d not in 0..4", p->sh_degree); return TSPLAT_EINVAL; }
+  if (p->sh_coeffs < 0 || p->sh_coeffs > 25) { set_error("sh_coeffs %d not in 0..25", p->sh_coeffs); return TSPLAT_EINVAL; }
+  if (p->sh_coeffs > 0) {
+    const int eff = (p->sh_degree >= 4 && !p->sh_l4) ? 3 : p->sh_degree;
+    if ((eff + 1) * (eff + 1) > p->sh_coeffs) {
+      set_error("sh_degree %d needs %d coefficients, got %d", p->sh_degree, (eff + 1) * (eff + 1), p->sh_coeffs);
+      return TSPLAT_EINVAL;
+    }
+  }
+  if (p->sh_layout != TSPLAT_SH_GM3 && p->sh_layout != TSPLAT_SH_G3M) { set_error("bad sh_layout"); return TSPLAT_EINVAL; }
+  if (p->cov_layout != TSPLAT_COV_TRIU6 && p->cov_layout != TSPLAT_COV_FULL9) { set_error("bad cov_layout"); return TSPLAT_EINVAL; }
+  if (p->depth_mode < TSPLAT_DEPTH_NONE || p->depth_mode > TSPLAT_DEPTH_LOG) { set_error("bad depth_mode"); return TSPLAT_EINVAL; }
+  if (d_cap < 1 || d_cap >= (1ull << 30)) { set_error("d_cap %llu not in [1, 2^30)", (unsigned long long)d_cap); return TSPLAT_EINVAL; }
+  if ((uint64_t)p->B * p->V * (uint64_t)p->G >= (1ull << 31)) { set_error("B*V*G too large"); return TSPLAT_EINVAL; }
+  const int tx = (p->W + kTile - 1) / kTile, ty = (p->H + kTile - 1) / kTile;
+  if (tx > 1023 || ty > 1023) { set_error("image too large (more than 1023 tiles per axis)"); return TSPLAT_EINVAL; }
+  if ((uint64_t)p->B * p->V * tx * ty >= (1ull << 31)) { set_error("too many (view, tile) pairs"); return TSPLAT_EINVAL; }
+  return TSPLAT_OK;
+}
+
+int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
+  memset(out, 0, sizeof(*out));
+  const uint64_t N = (uint64_t)p.B * p.V, G = (uint64_t)p.G, NG = N * G;
+  const int tx = (p.W + kTile - 1) / kTile, ty = (p.H + kTile - 1) / kTile;
+  const uint64_t T = (uint64_t)tx * ty, P = (uint64_t)p.H * p.W;
+  uint64_t off = 0;
+  auto take = [&](uint64_t bytes) { const uint64_t o = off; off = (off + bytes + 255) & ~(uint64_t)255; return o; };
+  TsplatLayout& L = out->pub;
+  out->num_scan_tiles = (int)((NG + kScanTile - 1) / kScanTile);
+  if (out->num_scan_tiles < 1) out->num_scan_tiles = 1;
+  out->num_sort_tiles = (int)((d_cap + kSortTile - 1) / kSortTile);
+  L.tiles_x = tx; L.tiles_y = ty;
+  L.sort_bits = 32 + (bits_for(N * T) > 0 ? bits_for(N * T) : 1);
+  L.sort_passes = (L.sort_bits + kRadixBits - 1) / kRadixBits;
+  // ---- region zeroed at the start of every forward ----
+  out->zero_begin = off;
+  L.status = take(sizeof(Control));
+  out->scan_state = take(8ull * out->num_scan_tiles);
+  out->sort_state = take(4ull * kRadix * out->num_sort_tiles * L.sort_passes);
+  L.ranges = take(8ull * N * T);
+  out->zero_end = off;
+  // ---- per (view, Gaussian) state ----
+  L.depths = take(4 * NG);
+  L.radii = take(4 * NG);
+  L.xy = take(8 * NG);
+  L.conic_opacity = take(16 * NG);
+  L.rgbd = take(16 * NG);
+  L.tiles_touched = take(4 * NG);
+  L.clamped = take(NG);
+  // ---- pair list (double-buffered for the radix passes) ----
+  const uint64_t k0 = take(8 * d_cap), k1 = take(8 * d_cap);
+  const uint64_t v0 = take(4 * d_cap), v1 = take(4 * d_cap);
+  const bool odd = L.sort_passes & 1;
+  L.keys = odd ? k1 : k0; out->keys_alt = odd ? k0 : k1;
+  L.vals = odd ? v1 : v0; out->vals_alt = odd ? v0 : v1;
+  out->rec0 = take(16 * d_cap);
+  out->rec1 = take(16 * d_cap);
+  out->rec2 = take(16 * d_cap);
+  // ---- per pixel ----
+  L.final_T = take(4 * N * P);
+  L.n_contrib = take(4 * N * P);
+  // ---- backward ----
+  L.grad_acc = take(4ull * kAccFloats * NG);
+  L.total_bytes = off;
+  return TSPLAT_OK;
+}
+
+Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
+  const TsplatLayout& L = F.pub;
+  char* b = static_cast<char*>(base);
+  Workspace w;
+  w.ctl = reinterpret_cast<Control*>(b + L.status);
+  w.depths = reinterpret_cast<float*>(b + L.depths);
+  w.radii = reinterpret_cast<int*>(b + L.radii);
+  w.xy = reinterpret_cast<float2*>(b + L.xy);
+  w.conic_opacity = reinterpret_cast<float4*>(b + L.conic_opacity);
+  w.rgbd = reinterpret_cast<float4*>(b + L.rgbd);
+  w.tiles_touched = reinterpret_cast<unsigned int*>(b + L.tiles_touched);
+  w.clamped = reinterpret_cast<unsigned char*>(b + L.clamped);
+  const bool odd = L.sort_passes & 1;  // buffer 0 is where bin_emit writes; sorted result lands in [passes & 1]
+  w.keys[0] = reinterpret_cast<unsigned long long*>(b + (odd ? F.keys_alt : L.keys));
+  w.keys[1] = reinterpret_cast<unsigned long long*>(b + (odd ? L.keys : F.keys_alt));
+  w.vals[0] = reinterpret_cast<unsigned int*>(b + (odd ? F.vals_alt : L.vals));
+  w.vals[1] = reinterpret_cast<unsigned int*>(b + (odd ? L.vals : F.vals_alt));
+  w.ranges = reinterpret_cast<uint2*>(b + L.ranges);
+  w.final_T = reinterpret_cast<float*>(b + L.final_T);
+  w.n_contrib = reinterpret_cast<unsigned int*>(b + L.n_contrib);
+  w.grad_acc = reinterpret_cast<float*>(b + L.grad_acc);
+  w.rec0 = reinterpret_cast<float4*>(b + F.rec0);
+  w.rec1 = reinterpret_cast<float4*>(b + F.rec1);
+  w.rec2 = reinterpret_cast<float4*>(b + F.rec2);
+  w.scan_state = reinterpret_cast<unsigned long long*>(b + F.scan_state);
+  w.sort_state = reinterpret_cast<unsigned int*>(b + F.sort_state);
+  w.d_cap = d_cap;
+  w.tiles_x = L.tiles_x; w.tiles_y = L.tiles_y; w.T = L.tiles_x * L.tiles_y; w.N = N;
+  w.sort_bits = L.sort_bits; w.sort_passes = L.sort_passes;
+  w.num_scan_tiles = F.num_scan_tiles; w.num_sort_tiles = F.num_sort_tiles;
+  return w;
+}
+
+static int cuda_fail(const char* what, cudaError_t e) {
+  set_error("%s: %s", what, cudaGetErrorString(e));
+  return TSPLAT_ECUDA;
+}
+
+static int prepare(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                   LayoutFull* F, Workspace* ws) {
+  int rc = validate(p, d_cap);
+  if (rc) return rc;
+  if (!workspace) { set_error("workspace is NULL"); return TSPLAT_EINVAL; }
+  if (reinterpret_cast<uintptr_t>(workspace) & 255u) { set_error("workspace must be 256-B aligned"); return TSPLAT_EINVAL; }
+  if (!p->means || !p->cov || !p->sh || !p->opacity || !p->cams) { set_error("NULL input pointer"); return TSPLAT_EINVAL; }
+  compute_layout(*p, d_cap, F);
+  if (F->pub.total_bytes > workspace_bytes) {
+    set_error("workspace too small: need %llu bytes, have %llu", (unsigned long long)F->pub.total_bytes,
+              (unsigned long long)workspace_bytes);
+    return TSPLAT_ENOSPC;
+  }
+  *ws = resolve(*F, workspace, d_cap, p->B * p->V);
+  return TSPLAT_OK;
+}
+
+}  // namespace tsplat
+
+using namespace tsplat;
+
+extern "C" {
+
+int tsplat_version(void) { return TSPLAT_VERSION; }
+const char* tsplat_last_error(void) { return g_err; }
+
+int tsplat_workspace_layout(const TsplatProblem* p, uint64_t d_cap, TsplatLayout* out) {
+  int rc = validate(p, d_cap);
+  if (rc) return rc;
+  if (!out) { set_error("out is NULL"); return TSPLAT_EINVAL; }
+  LayoutFull F;
+  compute_layout(*p, d_cap, &F);
+  *out = F.pub;
+  return TSPLAT_OK;
+}
+
+int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                   float* out_color, float* out_depth, int32_t* out_radii, void* cuda_stream) {
+  LayoutFull F;
+  Workspace ws;
+  int rc = prepare(p, workspace, workspace_bytes, d_cap, &F, &ws);
+  if (rc) return rc;
+  if (!out_color) { set_error("out_color is NULL"); return TSPLAT_EINVAL; }
+  if (p->depth_mode != TSPLAT_DEPTH_NONE && !out_depth) { set_error("depth_mode set but out_depth is NULL"); return TSPLAT_EINVAL; }
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  cudaError_t e = cudaMemsetAsync(static_cast<char*>(workspace) + F.zero_begin, 0, F.zero_end - F.zero_begin, st);
+  if (e != cudaSuccess) return cuda_fail("memset(control)", e);
+  if (p->G == 0) {
+    // nothing to draw: background only.  num_rendered stays 0; the render kernel sees empty ranges.
+  } else {
+    if ((e = launch_preprocess(*p, ws, out_radii, st)) != cudaSuccess) return cuda_fail("preprocess", e);
+    if ((e = launch_binning(*p, ws, st)) != cudaSuccess) return cuda_fail("binning", e);
+  }
+  if ((e = launch_render_forward(*p, ws, out_color, out_depth, st)) != cudaSuccess) return cuda_fail("render_forward", e);
+  return TSPLAT_OK;
+}
+
+int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                    const float* dL_dcolor, const float* dL_ddepth, float* dL_dmeans, float* dL_dcov,
+                    float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, void* cuda_stream) {
+  LayoutFull F;
+  Workspace ws;
+  int rc = prepare(p, workspace, workspace_bytes, d_cap, &F, &ws);
+  if (rc) return rc;
+  if (!dL_dcolor || !dL_dmeans || !dL_dcov || !dL_dsh || !dL_dopacity) { set_error("NULL gradient pointer"); return TSPLAT_EINVAL; }
+  if (p->depth_mode != TSPLAT_DEPTH_NONE && !dL_ddepth) { set_error("depth_mode set but dL_ddepth is NULL"); return TSPLAT_EINVAL; }
+  if (p->G == 0) return TSPLAT_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  const uint64_t NG = (uint64_t)p->B * p->V * p->G;
+  cudaError_t e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * NG, st);
+  if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
+  if ((e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, st)) != cudaSuccess) return cuda_fail("render_backward", e);
+  if ((e = launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D, st)) != cudaSuccess)
+    return cuda_fail("preprocess_backward", e);
+  return TSPLAT_OK;
+}
+
+int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix, const float* projmatrix,
+                        uint8_t* present, void* cuda_stream) {
+  (void)projmatrix;  // the reference's frustum test only uses the view matrix (SURVEY A.2 in_frustum)
+  if (G < 0 || !means || !viewmatrix || !present) { set_error("bad mark_visible arguments"); return TSPLAT_EINVAL; }
+  cudaError_t e = launch_mark_visible(G, means, viewmatrix, present, static_cast<cudaStream_t>(cuda_stream));
+  if (e != cudaSuccess) return cuda_fail("mark_visible", e);
+  return TSPLAT_OK;
+}
+
+int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream) {
+  if (!workspace || !status_host) { set_error("bad status_read arguments"); return TSPLAT_EINVAL; }
+  cudaError_t e = cudaMemcpyAsync(status_host, workspace, sizeof(TsplatStatus), cudaMemcpyDeviceToHost,
+                                  static_cast<cudaStream_t>(cuda_stream));
+  if (e != cudaSuccess) return cuda_fail("status_read", e);
+  return TSPLAT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,163 @@
+// common.cuh — shared declarations for libtsplat.so (sm_100a only).
+// Internal header: the public boundary is include/tsplat.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/tsplat.h"
+
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ < 1000)
+#error "libtsplat is written for sm_100a (B200) only"
+#endif
+
+namespace tsplat {
+
+constexpr int kTile = TSPLAT_TILE;          // 16x16 pixels per tile (parity contract)
+constexpr int kTilePix = kTile * kTile;     // 256
+constexpr int kPreBlock = 128;              // Gaussians per preprocess CTA
+constexpr int kScanThreads = 256;
+constexpr int kScanItems = 4;               // (view, Gaussian) items per thread in bin_emit
+constexpr int kScanTile = kScanThreads * kScanItems;
+constexpr int kSortThreads = 256;
+constexpr int kSortKpt = 12;                // keys per thread per onesweep tile
+constexpr int kSortTile = kSortThreads * kSortKpt;
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kMaxPasses = 8;
+constexpr int kBatch = 256;                 // list entries staged per TMA batch in the render kernels
+constexpr int kAccFloats = 12;              // screen-space gradient accumulators per (view, Gaussian)
+
+// Device-side control block at the start of the workspace (superset of TsplatStatus).
+struct Control {
+  unsigned long long num_rendered;  // D (uncapped)
+  unsigned int overflow;
+  unsigned int reserved;
+  unsigned int scan_tile_counter;   // dynamic tile ids for bin_emit
+  unsigned int sort_tile_counter[kMaxPasses];
+  unsigned int pad[3];
+  unsigned int hist[kMaxPasses][kRadix];  // global digit histograms (onesweep: one upfront sweep)
+};
+
+// Resolved workspace pointers (host-side struct passed to kernels by value).
+struct Workspace {
+  Control* ctl;
+  float* depths;
+  int* radii;
+  float2* xy;
+  float4* conic_opacity;
+  float4* rgbd;
+  unsigned int* tiles_touched;
+  unsigned char* clamped;
+  unsigned long long* keys[2];
+  unsigned int* vals[2];
+  uint2* ranges;
+  float* final_T;
+  unsigned int* n_contrib;
+  float* grad_acc;
+  float4* rec0;  // x, y, conic.x, conic.y                      (sorted order)
+  float4* rec1;  // conic.z, opacity, r, g
+  float4* rec2;  // b, depth feature, bits(Gaussian id), 0
+  unsigned long long* scan_state;  // decoupled look-back words for bin_emit
+  unsigned int* sort_state;        // [passes][sort tiles][256]
+  unsigned long long d_cap;
+  int tiles_x, tiles_y, T, N;      // tiles per view, views per call
+  int sort_bits, sort_passes;
+  int num_scan_tiles, num_sort_tiles;
+};
+
+struct LayoutFull {
+  TsplatLayout pub;
+  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, scan_state, sort_state, zero_begin, zero_end;
+  int num_scan_tiles, num_sort_tiles;
+};
+
+int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out);
+Workspace resolve(const LayoutFull& L, void* base, uint64_t d_cap, int N);
+void set_error(const char* fmt, ...);
+
+// stage launchers (each only enqueues on `st`)
+cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, cudaStream_t st);
+cudaError_t launch_binning(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color,
+                                  float* out_depth, cudaStream_t st);
+cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,
+                                   const float* dL_ddepth, cudaStream_t st);
+cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& ws, float* dL_dmeans,
+                                       float* dL_dcov, float* dL_dsh, float* dL_dopacity,
+                                       float* dL_dmeans2D, cudaStream_t st);
+cudaError_t launch_mark_visible(int G, const float* means, const float* view, uint8_t* present,
+                                cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+// PTX helpers: mbarrier + 1-D bulk async copy (TMA, SASS UBLKCP) — sm_90+/sm_100a.
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+// global -> shared::cta bulk copy; bytes % 16 == 0, both addresses 16-B aligned.
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+// shared::cta -> global bulk copy (bulk async-group completion)
+__device__ __forceinline__ void bulk_s2g(void* gmem_dst, const void* smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst),
+               "r"(smem_u32(smem_src)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+// make generic-proxy smem writes visible to the async proxy before a bulk store
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+__device__ __forceinline__ unsigned long long ld_relaxed_u64(const unsigned long long* p) {
+  unsigned long long v;
+  asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u64(unsigned long long* p, unsigned long long v) {
+  asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_relaxed_u32(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_relaxed_u32(unsigned int* p, unsigned int v) {
+  asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+#endif  // __CUDACC__
+
+}  // namespace tsplat

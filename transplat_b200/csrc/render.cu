@@ -1,0 +1,343 @@
+// render.cu — per-16x16-tile alpha compositing, forward and backward.
+//
+// One CTA per (view, tile); grid = N*T, so every view of the call renders in one launch.  The
+// tile's slice of the depth-sorted record arrays (3 x float4 per entry, written by
+// ranges_gather_kernel) is contiguous, so batches of 256 entries are staged into shared memory
+// with 1-D TMA bulk copies completing on mbarriers, double-buffered: thread 0 issues batch b+1
+// while all 8 warps composite batch b from shared-memory broadcasts.  Colour (3 channels) and the
+// depth feature (4th channel) are composited in the same pass (the reference renders depth with a
+// second full pass, cuda_splatting.py:404).  Termination is voted per warp (__all_sync) and per
+// CTA (__syncthreads_count), as the reference does per CTA.
+#include "common.cuh"
+
+namespace tsplat {
+
+struct RenderSmem {
+  float4 r0[2][kBatch];
+  float4 r1[2][kBatch];
+  float4 r2[2][kBatch];
+  uint64_t full[2];
+};
+
+template <class Smem>
+__device__ __forceinline__ void issue_batch(Smem& s, int buf, const Workspace& ws, unsigned int first,
+                                            unsigned int cnt) {
+  const uint32_t bytes = cnt * 16u;
+  mbar_expect_tx(&s.full[buf], 3u * bytes);
+  bulk_g2s(s.r0[buf], ws.rec0 + first, bytes, &s.full[buf]);
+  bulk_g2s(s.r1[buf], ws.rec1 + first, bytes, &s.full[buf]);
+  bulk_g2s(s.r2[buf], ws.rec2 + first, bytes, &s.full[buf]);
+}
+
+template <int CH>
+__global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, int H, int W,
+                                                                  const TsplatCamera* __restrict__ cams,
+                                                                  float* __restrict__ out_color,
+                                                                  float* __restrict__ out_depth) {
+  __shared__ __align__(128) RenderSmem s;
+  const int tid = threadIdx.x;
+  const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
+  const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
+  // warp w covers rows 2w, 2w+1 of the tile: 16 consecutive pixels per half-warp
+  const int px = tx * kTile + (tid & 15), py = ty * kTile + (tid >> 4);
+  const bool inside = px < W && py < H;
+  const float pxf = (float)px, pyf = (float)py;
+  const uint2 range = ws.ranges[blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int nb = (total + kBatch - 1) / kBatch;
+
+  if (tid == 0) {
+    mbar_init(&s.full[0], 1);
+    mbar_init(&s.full[1], 1);
+    mbar_fence_init();
+    if (nb > 0) issue_batch(s, 0, ws, range.x, (unsigned)min(kBatch, total));
+  }
+  __syncthreads();
+
+  float T = 1.0f;
+  float C[CH];
+#pragma unroll
+  for (int ch = 0; ch < CH; ch++) C[ch] = 0.0f;
+  unsigned int contributor = 0, last_contributor = 0;
+  bool done = !inside;
+  int consumed = 0;  // batches whose barrier has been waited on
+
+  for (int b = 0; b < nb; b++) {
+    // everyone is past batch b-1 => buffer (b+1)&1 is free; also the CTA-wide termination vote
+    const int num_done = __syncthreads_count(done);
+    if (num_done == kTilePix) break;
+    if (tid == 0 && b + 1 < nb)
+      issue_batch(s, (b + 1) & 1, ws, range.x + (unsigned)(b + 1) * kBatch,
+                  (unsigned)min(kBatch, total - (b + 1) * kBatch));
+    const int buf = b & 1;
+    mbar_wait(&s.full[buf], (b >> 1) & 1);
+    consumed = b + 1;
+    const int cnt = min(kBatch, total - b * kBatch);
+    for (int j = 0; j < cnt; j++) {
+      if ((j & 7) == 0 && __all_sync(0xffffffffu, done)) break;  // warp-level early out
+      contributor++;
+      const float4 a0 = s.r0[buf][j];
+      const float4 a1 = s.r1[buf][j];
+      const float dx = a0.x - pxf, dy = a0.y - pyf;
+      const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+      if (done || power > 0.0f) continue;
+      const float alpha = fminf(0.99f, a1.y * __expf(power));
+      if (alpha < 1.0f / 255.0f) continue;
+      const float test_T = T * (1.0f - alpha);
+      if (test_T < 0.0001f) { done = true; continue; }
+      const float4 a2 = s.r2[buf][j];
+      const float w = alpha * T;
+      C[0] += a1.z * w;
+      C[1] += a1.w * w;
+      C[2] += a2.x * w;
+      if (CH == 4) C[3] += a2.y * w;
+      T = test_T;
+      last_contributor = contributor;
+    }
+  }
+  // never leave the CTA with a bulk copy still in flight into its shared memory
+  // (if the loop broke at the vote of batch `consumed`, that batch's copy was already issued)
+  if (tid == 0 && consumed < nb) mbar_wait(&s.full[consumed & 1], (consumed >> 1) & 1);
+  if (inside) {
+    const size_t pix = (size_t)py * W + px;
+    const size_t P = (size_t)H * W;
+    const float* bg = cams[n].bg;
+    ws.final_T[n * P + pix] = T;
+    ws.n_contrib[n * P + pix] = last_contributor;
+    out_color[(n * 3 + 0) * P + pix] = C[0] + T * __ldg(bg + 0);
+    out_color[(n * 3 + 1) * P + pix] = C[1] + T * __ldg(bg + 1);
+    out_color[(n * 3 + 2) * P + pix] = C[2] + T * __ldg(bg + 2);
+    if (CH == 4) {  // mean over three identical channels (cuda_splatting.py:417)
+      const float x = C[3];
+      out_depth[n * P + pix] = __fdiv_rn(__fadd_rn(__fadd_rn(x, x), x), 3.0f);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Backward: back-to-front over the same list.  Per entry the 10 gradient components
+// (mean2D.xy, conic.xyw, opacity, colour[CH]) are pre-reduced over the 32 pixels of each warp with
+// a 12-shuffle transpose-reduction, added into a per-batch shared-memory accumulator
+// (red.shared), and flushed with ONE global reduction per (tile, Gaussian, component) instead of
+// one atomic per (pixel, Gaussian, component) as the reference does.
+// ---------------------------------------------------------------------------------------------
+struct RenderBwdSmem {
+  float4 r0[2][kBatch];
+  float4 r1[2][kBatch];
+  float4 r2[2][kBatch];
+  float acc[kBatch][kAccFloats];
+  uint64_t full[2];
+};
+
+// Reduce v[0..9] over the warp.  On return lane L holds in `out` the full sum of component
+// comp_of_lane(L) (see below); lanes L and L^1 hold the same component.
+__device__ __forceinline__ float warp_transpose_reduce10(float (&v)[10], int lane) {
+  const unsigned int full = 0xffffffffu;
+  // round 1 (xor 16): 10 -> 5.  upper half-warp keeps 5..9, lower keeps 0..4
+  float a[6];
+  {
+    const bool up = lane & 16;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+      const float send = up ? v[i] : v[i + 5];
+      const float keep = up ? v[i + 5] : v[i];
+      a[i] = keep + __shfl_xor_sync(full, send, 16);
+    }
+    a[5] = 0.0f;
+  }
+  // round 2 (xor 8): 6 -> 3
+  float b[4];
+  {
+    const bool up = lane & 8;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+      const float send = up ? a[i] : a[i + 3];
+      const float keep = up ? a[i + 3] : a[i];
+      b[i] = keep + __shfl_xor_sync(full, send, 8);
+    }
+    b[3] = 0.0f;
+  }
+  // round 3 (xor 4): 4 -> 2
+  float c[2];
+  {
+    const bool up = lane & 4;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float send = up ? b[i] : b[i + 2];
+      const float keep = up ? b[i + 2] : b[i];
+      c[i] = keep + __shfl_xor_sync(full, send, 4);
+    }
+  }
+  // round 4 (xor 2): 2 -> 1
+  float d;
+  {
+    const bool up = lane & 2;
+    const float send = up ? c[0] : c[1];
+    const float keep = up ? c[1] : c[0];
+    d = keep + __shfl_xor_sync(full, send, 2);
+  }
+  d += __shfl_xor_sync(full, d, 1);
+  return d;
+}
+// component index held by `lane` after warp_transpose_reduce10, or -1 (padding slot)
+__device__ __forceinline__ int comp_of_lane(int lane) {
+  const int h16 = (lane >> 4) & 1, h8 = (lane >> 3) & 1, h4 = (lane >> 2) & 1, h2 = (lane >> 1) & 1;
+  // round 3 index within b[0..3]: i3 = h2 + 2*h4 ; round 2 index within a[0..5]: i2 = i3' + 3*h8
+  const int ib = h2 + 2 * h4;          // slot in b[] (0..3), 3 is padding
+  if (ib == 3) return -1;
+  const int ia = ib + 3 * h8;          // slot in a[] (0..5), 5 is padding
+  if (ia == 5) return -1;
+  return ia + 5 * h16;                 // slot in v[] (0..9)
+}
+
+template <int CH>
+__global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws, int H, int W, int G,
+                                                                   const TsplatCamera* __restrict__ cams,
+                                                                   const float* __restrict__ dL_dcolor,
+                                                                   const float* __restrict__ dL_ddepth) {
+  extern __shared__ __align__(128) unsigned char bsmem_raw[];
+  RenderBwdSmem& s = *reinterpret_cast<RenderBwdSmem*>(bsmem_raw);
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
+  const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
+  const int px = tx * kTile + (tid & 15), py = ty * kTile + (tid >> 4);
+  const bool inside = px < W && py < H;
+  const float pxf = (float)px, pyf = (float)py;
+  const uint2 range = ws.ranges[blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int nb = (total + kBatch - 1) / kBatch;
+  const size_t P = (size_t)H * W;
+  const size_t pix = (size_t)py * W + px;
+
+  // batch b (b = 0 is the END of the list) covers sorted entries [lo_b, hi_b)
+  auto batch_hi = [&](int b) { return (int)range.y - b * kBatch; };
+  auto batch_lo = [&](int b) { return max((int)range.x, (int)range.y - (b + 1) * kBatch); };
+
+  if (tid == 0) {
+    mbar_init(&s.full[0], 1);
+    mbar_init(&s.full[1], 1);
+    mbar_fence_init();
+    if (nb > 0) issue_batch(s, 0, ws, (unsigned)batch_lo(0), (unsigned)(batch_hi(0) - batch_lo(0)));
+  }
+  for (int i = tid; i < kBatch * kAccFloats; i += kTilePix) (&s.acc[0][0])[i] = 0.0f;
+  __syncthreads();
+
+  const float T_final = inside ? ws.final_T[n * P + pix] : 0.0f;
+  float T = T_final;
+  const int last_contributor = inside ? (int)ws.n_contrib[n * P + pix] : 0;
+  float accum_rec[CH], last_color[CH], dL_dpix[CH];
+#pragma unroll
+  for (int ch = 0; ch < CH; ch++) { accum_rec[ch] = 0.0f; last_color[ch] = 0.0f; dL_dpix[ch] = 0.0f; }
+  if (inside) {
+#pragma unroll
+    for (int ch = 0; ch < 3; ch++) dL_dpix[ch] = dL_dcolor[(n * 3 + ch) * P + pix];
+    if (CH == 4) dL_dpix[3] = dL_ddepth[n * P + pix];
+  }
+  const float* bgp = cams[n].bg;
+  // bg of the fused depth channel is 0 (render_depth_cuda passes zeros, cuda_splatting.py:410)
+  const float bg_dot = __ldg(bgp) * dL_dpix[0] + __ldg(bgp + 1) * dL_dpix[1] + __ldg(bgp + 2) * dL_dpix[2];
+  float last_alpha = 0.0f;
+  const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
+  const int my_comp = comp_of_lane(lane);
+
+  for (int b = 0; b < nb; b++) {
+    const int buf = b & 1;
+    const int lo = batch_lo(b), hi = batch_hi(b), cnt = hi - lo;
+    if (tid == 0 && b + 1 < nb)  // buffer (b+1)&1 was released by the barrier that ended batch b-1
+      issue_batch(s, (b + 1) & 1, ws, (unsigned)batch_lo(b + 1), (unsigned)(batch_hi(b + 1) - batch_lo(b + 1)));
+    mbar_wait(&s.full[buf], (b >> 1) & 1);
+    // entries of this batch with list position >= the warp's deepest contributor are skipped whole
+    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+    for (int j = cnt - 1; j >= 0; j--) {
+      const int pos = lo + j - (int)range.x;  // 0-based position in the tile's list
+      if (pos >= warp_last) continue;         // warp-uniform
+      const float4 a0 = s.r0[buf][j];
+      const float4 a1 = s.r1[buf][j];
+      const float dx = a0.x - pxf, dy = a0.y - pyf;
+      const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+      const float Gv = __expf(power);
+      const float alpha = fminf(0.99f, a1.y * Gv);
+      const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+      if (!__any_sync(0xffffffffu, valid)) continue;
+      float v[10];
+#pragma unroll
+      for (int k = 0; k < 10; k++) v[k] = 0.0f;
+      if (valid) {
+        const float4 a2 = s.r2[buf][j];
+        const float col[4] = {a1.z, a1.w, a2.x, a2.y};
+        T = T / (1.0f - alpha);
+        const float dchannel_dcolor = alpha * T;
+        float dL_dalpha = 0.0f;
+#pragma unroll
+        for (int ch = 0; ch < CH; ch++) {
+          const float c = col[ch];
+          accum_rec[ch] = last_alpha * last_color[ch] + (1.0f - last_alpha) * accum_rec[ch];
+          last_color[ch] = c;
+          dL_dalpha += (c - accum_rec[ch]) * dL_dpix[ch];
+          v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
+        }
+        dL_dalpha *= T;
+        last_alpha = alpha;
+        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
+        const float dL_dG = a1.y * dL_dalpha;
+        const float gdx = Gv * dx, gdy = Gv * dy;
+        const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
+        const float dG_ddely = -gdy * a1.x - gdx * a0.w;
+        v[0] = dL_dG * dG_ddelx * ddelx_dx;
+        v[1] = dL_dG * dG_ddely * ddely_dy;
+        v[2] = -0.5f * gdx * dx * dL_dG;
+        v[3] = -0.5f * gdx * dy * dL_dG;
+        v[4] = -0.5f * gdy * dy * dL_dG;
+        v[5] = Gv * dL_dalpha;
+      }
+      const float r = warp_transpose_reduce10(v, lane);
+      if (my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9)) atomicAdd(&s.acc[j][my_comp], r);
+    }
+    __syncthreads();  // all warps finished batch b: accumulators complete, buffer b&1 free
+    if (tid < cnt) {
+      const unsigned int id = __float_as_uint(s.r2[buf][tid].z);
+      float* dst = ws.grad_acc + ((size_t)n * G + id) * kAccFloats;
+      bool any = false;
+      float q[10];
+#pragma unroll
+      for (int k = 0; k < 10; k++) { q[k] = s.acc[tid][k]; any |= (q[k] != 0.0f); s.acc[tid][k] = 0.0f; }
+      if (any) {
+#pragma unroll
+        for (int k = 0; k < 10; k++)
+          if (k < 6 + CH) atomicAdd(dst + k, q[k]);
+      }
+    }
+    __syncthreads();  // accumulators re-zeroed and record ids read before the buffer is reused
+  }
+}
+
+cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color, float* out_depth,
+                                  cudaStream_t st) {
+  const int grid = ws.N * ws.T;
+  if (grid == 0) return cudaSuccess;
+  if (p.depth_mode != TSPLAT_DEPTH_NONE)
+    render_forward_kernel<4><<<grid, kTilePix, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
+  else
+    render_forward_kernel<3><<<grid, kTilePix, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,
+                                   const float* dL_ddepth, cudaStream_t st) {
+  const int grid = ws.N * ws.T;
+  if (grid == 0) return cudaSuccess;
+  const int smem = (int)sizeof(RenderBwdSmem);
+  cudaError_t e;
+  if (p.depth_mode != TSPLAT_DEPTH_NONE) {
+    e = cudaFuncSetAttribute(render_backward_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    render_backward_kernel<4><<<grid, kTilePix, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
+  } else {
+    e = cudaFuncSetAttribute(render_backward_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return e;
+    render_backward_kernel<3><<<grid, kTilePix, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace tsplat

@@ -1,0 +1,171 @@
+"""Level-2 boundary: the decoder of TranSplat's render path with the reference's names,
+signatures and error behaviour
+
+  Gaussians                         src/model/types.py:7-12
+  DecoderOutput, DepthRenderingMode src/model/decoder/decoder.py:12-22
+  render_cuda                       src/model/decoder/cuda_splatting.py:56-136
+  render_depth_cuda                 src/model/decoder/cuda_splatting.py:375-417
+  render_cuda_with_stats            src/model/decoder/cuda_splatting.py:235-372
+  DecoderSplattingCUDA              src/model/decoder/decoder_splatting_cuda.py:26-146
+  DECODERS / get_decoder            src/model/decoder/__init__.py:5-13
+
+but batched: one library call renders every (scene, view) of the batch, colour and depth come
+from ONE pass, the Gaussians are never ``repeat``-ed per view (decoder_splatting_cuda.py:59-62
+materialises v copies), SH is read in the encoder's [G,3,d_sh] layout (no transpose copy,
+cuda_splatting.py:84), covariances in their [G,3,3] layout (no triu gather, :124), and nothing
+synchronises the host (the reference calls .item() twice per view, :111-112).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from math import isqrt
+from typing import Literal, Optional
+
+import torch
+from torch import Tensor, nn
+
+from ._lib import COV_FULL9, DEPTH_MODES, SH_G3M
+from .cameras import pack_cameras
+from .rasterize import RenderConfig, rasterize
+
+DepthRenderingMode = Literal["depth", "log", "disparity", "relative_disparity"]
+
+
+@dataclass
+class Gaussians:
+    means: Tensor        # [batch, gaussian, 3]
+    covariances: Tensor  # [batch, gaussian, 3, 3]
+    harmonics: Tensor    # [batch, gaussian, 3, d_sh]
+    opacities: Tensor    # [batch, gaussian]
+
+
+@dataclass
+class DecoderOutput:
+    color: Tensor            # [batch, view, 3, height, width]
+    depth: Optional[Tensor]  # [batch, view, height, width]
+
+
+@dataclass
+class GaussianContributionStats:
+    """cuda_splatting.py:235-254 (same field names)."""
+    total_gaussians: int
+    visible_gaussians: int            # radii > 0
+    high_contribution_gaussians: int  # visible and opacity >= threshold
+    visible_ratio: float
+    high_contribution_ratio: float
+    opacity_threshold: float
+    radii: Optional[Tensor] = None
+
+
+def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
+                 image_shape: tuple, background_color: Tensor, depth_mode: Optional[str] = None,
+                 scale_invariant: bool = True, want_radii: bool = False, check: Optional[str] = None):
+    """The batched entry point.  extrinsics [b,v,4,4], intrinsics [b,v,3,3], near/far [b,v],
+    background_color [3] or [b*v,3].  Returns colour [b,v,3,h,w], depth [b,v,h,w]|None, radii [b,v,G]|None."""
+    b, v = extrinsics.shape[:2]
+    h, w = image_shape
+    if depth_mode is not None and depth_mode not in DEPTH_MODES:
+        raise ValueError(f"unknown depth_mode {depth_mode!r}")
+    d_sh = gaussians.harmonics.shape[-1]
+    degree = isqrt(d_sh) - 1
+    bg = background_color if background_color.dim() == 2 else background_color.expand(b * v, 3)
+    cams = pack_cameras(extrinsics.reshape(b * v, 4, 4), intrinsics.reshape(b * v, 3, 3),
+                        near.reshape(b * v), far.reshape(b * v), bg, scale_invariant=scale_invariant)
+    cfg = RenderConfig(H=h, W=w, V=v, sh_degree=degree, sh_layout=SH_G3M, cov_layout=COV_FULL9,
+                       depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check)
+    color, depth, radii = rasterize(gaussians.means, gaussians.covariances, gaussians.harmonics,
+                                    gaussians.opacities, cams, cfg)
+    color = color.reshape(b, v, 3, h, w)
+    depth = depth.reshape(b, v, h, w) if depth is not None else None
+    radii = radii.reshape(b, v, -1) if radii is not None else None
+    return color, depth, radii
+
+
+def render_cuda(extrinsics, intrinsics, near, far, image_shape, background_color, gaussian_means,
+                gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities,
+                scale_invariant: bool = True, use_sh: bool = True) -> Tensor:
+    """Signature of cuda_splatting.py:56-69: every argument has a leading "batch" axis that is
+    (scene x view) flattened, Gaussians already repeated per view.  Each batch entry is rendered as
+    its own one-view scene, in one library call."""
+    assert use_sh or gaussian_sh_coefficients.shape[-1] == 1
+    b = extrinsics.shape[0]
+    g = Gaussians(gaussian_means, gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities)
+    if not use_sh:
+        raise NotImplementedError("use_sh=False: pass colours as degree-0 harmonics instead")
+    color, _, _ = render_views(g, extrinsics[:, None], intrinsics[:, None], near[:, None], far[:, None],
+                               image_shape, background_color, None, scale_invariant)
+    return color.reshape(b, 3, *image_shape)
+
+
+def render_depth_cuda(extrinsics, intrinsics, near, far, image_shape, gaussian_means, gaussian_covariances,
+                      gaussian_opacities, scale_invariant: bool = True, mode: DepthRenderingMode = "depth") -> Tensor:
+    """Signature of cuda_splatting.py:375-386.  The depth channel is composited by the same kernel
+    as colour; the colour written alongside it here comes from zero harmonics and is discarded."""
+    b, G = gaussian_means.shape[:2]
+    zeros = torch.zeros((b, G, 3, 1), dtype=torch.float32, device=gaussian_means.device)
+    g = Gaussians(gaussian_means, gaussian_covariances, zeros, gaussian_opacities)
+    bg = torch.zeros((b, 3), dtype=torch.float32, device=gaussian_means.device)
+    _, depth, _ = render_views(g, extrinsics[:, None], intrinsics[:, None], near[:, None], far[:, None],
+                               image_shape, bg, mode, scale_invariant)
+    return depth.reshape(b, *image_shape)
+
+
+class DecoderSplattingCUDA(nn.Module):
+    """decoder_splatting_cuda.py:26-146 — same constructor shape (cfg, dataset_cfg) where
+    ``dataset_cfg.background_color`` is read, same forward/render_depth/forward_with_gaussian_stats."""
+
+    def __init__(self, cfg=None, dataset_cfg=None, background_color=(0.0, 0.0, 0.0)) -> None:
+        super().__init__()
+        self.cfg = cfg
+        self.dataset_cfg = dataset_cfg
+        if dataset_cfg is not None and hasattr(dataset_cfg, "background_color"):
+            background_color = dataset_cfg.background_color
+        self.register_buffer("background_color", torch.tensor(background_color, dtype=torch.float32),
+                             persistent=False)
+
+    def forward(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
+                image_shape: tuple, depth_mode: Optional[DepthRenderingMode] = None) -> DecoderOutput:
+        color, depth, _ = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
+                                       self.background_color, depth_mode)
+        return DecoderOutput(color, depth)
+
+    def render_depth(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
+                     image_shape: tuple, mode: DepthRenderingMode = "depth") -> Tensor:
+        _, depth, _ = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
+                                   torch.zeros_like(self.background_color), mode)
+        return depth
+
+    def forward_with_gaussian_stats(self, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
+                                    depth_mode: Optional[DepthRenderingMode] = None,
+                                    opacity_threshold: float = 0.01):
+        """decoder_splatting_cuda.py:99-146 / cuda_splatting.py:353-369: per-view contribution
+        statistics from ``radii`` (the only consumer of radii in the reference)."""
+        b, v = extrinsics.shape[:2]
+        color, depth, radii = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
+                                           self.background_color, depth_mode, want_radii=True)
+        stats = []
+        visible = radii > 0
+        high = visible & (gaussians.opacities >= opacity_threshold)[:, None, :]
+        n_visible = visible.sum(dim=-1).cpu()
+        n_high = high.sum(dim=-1).cpu()
+        G = radii.shape[-1]
+        for i in range(b):
+            for j in range(v):
+                nv, nh = int(n_visible[i, j]), int(n_high[i, j])
+                stats.append(GaussianContributionStats(
+                    total_gaussians=G, visible_gaussians=nv, high_contribution_gaussians=nh,
+                    visible_ratio=nv / G if G > 0 else 0.0, high_contribution_ratio=nh / G if G > 0 else 0.0,
+                    opacity_threshold=opacity_threshold, radii=radii[i, j].clone()))
+        return DecoderOutput(color, depth), stats
+
+
+@dataclass
+class DecoderSplattingCUDACfg:
+    name: Literal["splatting_cuda"]
+
+
+DECODERS = {"splatting_cuda": DecoderSplattingCUDA}
+
+
+def get_decoder(decoder_cfg, dataset_cfg):
+    return DECODERS[decoder_cfg.name](decoder_cfg, dataset_cfg)

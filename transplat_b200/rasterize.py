@@ -1,0 +1,267 @@
+"""torch.autograd.Function over the C-ABI of libtsplat.so: one call renders B scenes x V views
+(colour and, optionally, the fused depth channel) and one backward call returns the gradients
+summed over views.  PyTorch is plumbing here: device memory, the current stream, autograd.
+
+Replaces ``_RasterizeGaussians`` of the reference's external extension; the
+level-1 wrapper with the extension's exact call surface is in ``rasterizer.py``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import COV_FULL9, COV_TRIU6, DEPTH_MODES, SH_G3M, SH_GM3, TsplatLayout, TsplatProblem, TsplatStatus
+
+# capacity of the (tile, Gaussian) pair list, in pairs per (view, Gaussian); grows when a call
+# reports that it came close (see _Capacity)
+_DEFAULT_PAIRS_PER_GAUSSIAN = float(os.environ.get("TSPLAT_PAIRS_PER_GAUSSIAN", "8"))
+_CHECK_MODE = os.environ.get("TSPLAT_CHECK", "deferred")  # "deferred" | "sync"
+
+
+class OverflowError_(RuntimeError):
+    pass
+
+
+class _Capacity:
+    """d_cap per problem shape.  The pair count D is only known on the device; every call copies
+    it back asynchronously and the NEXT call of the same shape grows the capacity if needed."""
+
+    def __init__(self):
+        self.cap = {}
+        self.pending = {}
+
+    def get(self, key, n_items):
+        self.poll(key)
+        if key not in self.cap:
+            self.cap[key] = min(max(int(_DEFAULT_PAIRS_PER_GAUSSIAN * n_items), 4096), (1 << 30) - 1)
+        return self.cap[key]
+
+    def poll(self, key, wait=False):
+        p = self.pending.get(key)
+        if p is None:
+            return None
+        host, event = p
+        if not wait and not event.query():
+            return None
+        event.synchronize()
+        del self.pending[key]
+        st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
+        if key in self.cap and st.num_rendered * 1.25 > self.cap[key]:
+            self.cap[key] = min(int(st.num_rendered * 1.6) + 4096, (1 << 30) - 1)
+        return st
+
+    def grow(self, key, num_rendered):
+        self.cap[key] = min(int(num_rendered * 1.6) + 4096, (1 << 30) - 1)
+
+
+_capacity = _Capacity()
+
+
+@dataclass
+class RenderConfig:
+    H: int
+    W: int
+    V: int                     # views per scene
+    sh_degree: int
+    sh_layout: int = SH_GM3
+    cov_layout: int = COV_TRIU6
+    depth_mode: int = 0
+    sh_l4: int = 1
+    want_radii: bool = False
+    want_means2d_grad: bool = False
+    check: str | None = None   # None -> TSPLAT_CHECK env ("deferred" default)
+    d_cap: int | None = None
+
+
+def _ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def _problem(cfg: RenderConfig, means, cov, sh, opacity, cams) -> TsplatProblem:
+    p = TsplatProblem()
+    B, G = means.shape[0], means.shape[1]
+    p.B, p.G, p.V, p.H, p.W = B, G, cfg.V, cfg.H, cfg.W
+    p.sh_degree = cfg.sh_degree
+    if sh.dim() == 3:      # colors_precomp [B,G,3]
+        p.sh_coeffs = 0
+    else:
+        p.sh_coeffs = sh.shape[2] if cfg.sh_layout == SH_GM3 else sh.shape[3]
+    p.sh_layout, p.cov_layout, p.depth_mode, p.sh_l4 = cfg.sh_layout, cfg.cov_layout, cfg.depth_mode, cfg.sh_l4
+    p.means, p.cov, p.sh, p.opacity, p.cams = (means.data_ptr(), cov.data_ptr(), sh.data_ptr(),
+                                               opacity.data_ptr(), cams.data_ptr())
+    return p
+
+
+class _State:
+    """What backward needs from forward: the opaque workspace and the problem description."""
+    __slots__ = ("problem", "workspace", "d_cap", "layout", "key", "tensors", "status_host", "event")
+
+
+def _check_inputs(means, cov, sh, opacity, cams, cfg):
+    if not means.is_cuda:
+        raise RuntimeError("transplat_b200 renders on a CUDA device only (no CPU fallback)")
+    for name, t in (("means", means), ("cov", cov), ("sh", sh), ("opacity", opacity), ("cams", cams)):
+        if t.dtype != torch.float32:
+            raise RuntimeError(f"{name} must be float32")
+        if t.device != means.device:
+            raise RuntimeError(f"{name} is on {t.device}, means on {means.device}")
+    if means.dim() != 3 or means.shape[-1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    B, G = means.shape[:2]
+    want_cov = (B, G, 6) if cfg.cov_layout == COV_TRIU6 else (B, G, 3, 3)
+    if tuple(cov.shape) != want_cov:
+        raise RuntimeError(f"covariance must have shape {want_cov}, got {tuple(cov.shape)}")
+    if tuple(opacity.shape) != (B, G):
+        raise RuntimeError(f"opacity must have shape {(B, G)}, got {tuple(opacity.shape)}")
+    if tuple(cams.shape) != (B * cfg.V, 64):
+        raise RuntimeError(f"cameras must have shape {(B * cfg.V, 64)}, got {tuple(cams.shape)}")
+
+
+def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
+    """Launch the forward pipeline; returns (color, depth|None, radii|None, state)."""
+    L = _lib.lib()
+    _check_inputs(means, cov, sh, opacity, cams, cfg)
+    means, cov, sh, opacity, cams = (t.contiguous() for t in (means, cov, sh, opacity, cams))
+    B, G = means.shape[:2]
+    N = B * cfg.V
+    dev = means.device
+    key = (dev.index, N, G, cfg.H, cfg.W)
+    check = cfg.check or _CHECK_MODE
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev)
+        while True:
+            d_cap = cfg.d_cap or _capacity.get(key, N * max(G, 1))
+            prob = _problem(cfg, means, cov, sh, opacity, cams)
+            layout = TsplatLayout()
+            _lib.check(L.tsplat_workspace_layout(C.byref(prob), d_cap, C.byref(layout)), "tsplat_workspace_layout")
+            ws = torch.empty(layout.total_bytes, dtype=torch.uint8, device=dev)
+            color = torch.empty((N, 3, cfg.H, cfg.W), dtype=torch.float32, device=dev)
+            depth = torch.empty((N, cfg.H, cfg.W), dtype=torch.float32, device=dev) if cfg.depth_mode else None
+            radii = torch.empty((N, G), dtype=torch.int32, device=dev) if cfg.want_radii else None
+            _lib.check(L.tsplat_forward(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
+                                        _ptr(depth), _ptr(radii), C.c_void_p(stream.cuda_stream)),
+                       "tsplat_forward")
+            host = torch.empty(16, dtype=torch.uint8, pin_memory=True)
+            _lib.check(L.tsplat_status_read(_ptr(ws), C.c_void_p(host.data_ptr()),
+                                            C.c_void_p(stream.cuda_stream)), "tsplat_status_read")
+            event = torch.cuda.Event()
+            event.record(stream)
+            if check == "sync":
+                event.synchronize()
+                st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
+                if st.overflow:
+                    if cfg.d_cap:
+                        raise OverflowError_(f"pair list overflow: D={st.num_rendered} > d_cap={d_cap}")
+                    _capacity.grow(key, st.num_rendered)
+                    continue
+            else:
+                _capacity.pending[key] = (host, event)
+            break
+    state = _State()
+    state.problem, state.workspace, state.d_cap, state.layout, state.key = prob, ws, d_cap, layout, key
+    state.tensors = (means, cov, sh, opacity, cams)
+    state.status_host, state.event = host, event
+    return color, depth, radii, state
+
+
+def read_status(state) -> TsplatStatus:
+    state.event.synchronize()
+    return TsplatStatus.from_buffer_copy(state.status_host.numpy().tobytes())
+
+
+def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
+    L = _lib.lib()
+    means, cov, sh, opacity, cams = state.tensors
+    st = read_status(state)  # the forward finished long ago: this does not stall the pipeline
+    if st.overflow:
+        raise OverflowError_(
+            f"pair list overflow in the forward pass: D={st.num_rendered} > d_cap={state.d_cap}; the rendered "
+            "images were incomplete.  Raise TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
+    dev = means.device
+    N = means.shape[0] * cfg.V
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev)
+        grad_color = grad_color.contiguous() if grad_color is not None else torch.zeros(
+            (N, 3, cfg.H, cfg.W), dtype=torch.float32, device=dev)
+        if cfg.depth_mode:
+            grad_depth = grad_depth.contiguous() if grad_depth is not None else torch.zeros(
+                (N, cfg.H, cfg.W), dtype=torch.float32, device=dev)
+        else:
+            grad_depth = None
+        g_means = torch.empty_like(means)
+        g_cov = torch.empty_like(cov)
+        g_sh = torch.empty_like(sh)
+        g_op = torch.empty_like(opacity)
+        g_m2d = (torch.empty((N, means.shape[1], 3), dtype=torch.float32, device=dev)
+                 if cfg.want_means2d_grad else None)
+        _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
+                                     state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
+                                     _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
+                   "tsplat_backward")
+    return g_means, g_cov, g_sh, g_op, g_m2d
+
+
+class _Rasterize(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, means, cov, sh, opacity, means2d, cams, cfg):
+        color, depth, radii, state = forward_raw(cfg, means, cov, sh, opacity, cams)
+        ctx.cfg, ctx.state = cfg, state
+        ctx.has_m2d = means2d is not None
+        ctx.m2d_shape = tuple(means2d.shape) if means2d is not None else None
+        outs = [color]
+        outs.append(depth if depth is not None else torch.empty(0, device=color.device))
+        outs.append(radii if radii is not None else torch.empty(0, dtype=torch.int32, device=color.device))
+        ctx.mark_non_differentiable(outs[2])
+        if depth is None:
+            ctx.mark_non_differentiable(outs[1])
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_depth, _grad_radii):
+        cfg = ctx.cfg
+        g_means, g_cov, g_sh, g_op, g_m2d = backward_raw(cfg, ctx.state, grad_color,
+                                                         grad_depth if cfg.depth_mode else None)
+        if ctx.has_m2d and g_m2d is not None:
+            g_m2d = g_m2d.reshape(ctx.m2d_shape)
+        return g_means, g_cov, g_sh, g_op, (g_m2d if ctx.has_m2d else None), None, None
+
+
+def rasterize(means, cov, sh, opacity, cams, cfg: RenderConfig, means2d=None):
+    """means [B,G,3], cov [B,G,6]|[B,G,3,3], sh [B,G,M,3]|[B,G,3,M]|[B,G,3], opacity [B,G],
+    cams [B*V,64] (cameras.pack_cameras) -> color [B*V,3,H,W], depth [B*V,H,W]|None, radii|None."""
+    color, depth, radii = _Rasterize.apply(means, cov, sh, opacity, means2d, cams, cfg)
+    return color, (depth if cfg.depth_mode else None), (radii if cfg.want_radii else None)
+
+
+def inspect_workspace(state) -> dict:
+    """Typed views of the inspectable workspace sections (parity tests).  Synchronises."""
+    lay, ws, p = state.layout, state.workspace, state.problem
+    N, G, H, W = p.B * p.V, p.G, p.H, p.W
+    T = lay.tiles_x * lay.tiles_y
+    st = read_status(state)
+    D = min(int(st.num_rendered), state.d_cap)
+
+    def sec(off, nbytes, dtype, shape):
+        return ws[off:off + nbytes].view(dtype).reshape(shape)
+
+    return {
+        "num_rendered": int(st.num_rendered), "overflow": int(st.overflow), "T": T,
+        "sort_bits": lay.sort_bits,
+        "depths": sec(lay.depths, 4 * N * G, torch.float32, (N, G)),
+        "radii": sec(lay.radii, 4 * N * G, torch.int32, (N, G)),
+        "xy": sec(lay.xy, 8 * N * G, torch.float32, (N, G, 2)),
+        "conic_opacity": sec(lay.conic_opacity, 16 * N * G, torch.float32, (N, G, 4)),
+        "rgbd": sec(lay.rgbd, 16 * N * G, torch.float32, (N, G, 4)),
+        "tiles_touched": sec(lay.tiles_touched, 4 * N * G, torch.int32, (N, G)),
+        "clamped": sec(lay.clamped, N * G, torch.uint8, (N, G)),
+        "keys": sec(lay.keys, 8 * D, torch.int64, (D,)),
+        "vals": sec(lay.vals, 4 * D, torch.int32, (D,)),
+        "ranges": sec(lay.ranges, 8 * N * T, torch.int32, (N, T, 2)),
+        "final_T": sec(lay.final_T, 4 * N * H * W, torch.float32, (N, H, W)),
+        "n_contrib": sec(lay.n_contrib, 4 * N * H * W, torch.int32, (N, H, W)),
+        "grad_acc": sec(lay.grad_acc, 48 * N * G, torch.float32, (N, G, 12)),
+    }
