@@ -165,6 +165,18 @@ int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix,
 /* Copies the status block to pinned/pageable host memory asynchronously on the stream. */
 int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream);
 
+/* Optional per-stage device timing (cudaEvents recorded on the caller's stream around each stage;
+ * process-global, off by default, a ring of the last 256 forward(+backward) calls).  Replaces
+ * nothing in the reference, which only has wall-clock NVTX ranges around the whole decoder
+ * (src/misc/benchmarker.py:44-145, model_wrapper.py:209).
+ * tsplat_profile_read synchronises on the recorded events and fills ms_host[0..8] with the SUM of
+ * each stage's durations over the recorded calls and ms_host[9] with the number of calls summed:
+ * 0 zero-fill, 1 preprocess, 2 bin_emit, 3 sort, 4 ranges_gather, 5 render_forward,
+ * 6 zero-fill (bwd), 7 render_backward, 8 preprocess_backward.  n must be >= 10. */
+#define TSPLAT_NUM_STAGES 9
+int tsplat_profile_enable(int on);
+int tsplat_profile_read(float* ms_host, int n);
+
 #ifdef __cplusplus
 }
 #endif

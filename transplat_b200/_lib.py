@@ -16,7 +16,8 @@ COV_TRIU6, COV_FULL9 = 0, 1
 DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
-           "tsplat_backward", "tsplat_mark_visible", "tsplat_status_read")
+           "tsplat_backward", "tsplat_mark_visible", "tsplat_status_read", "tsplat_profile_enable",
+           "tsplat_profile_read")
 
 
 class TsplatProblem(C.Structure):
@@ -67,6 +68,8 @@ def lib():
                                       C.c_void_p, C.c_void_p, C.c_void_p]
         L.tsplat_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.tsplat_status_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_profile_enable.argtypes = [C.c_int]
+        L.tsplat_profile_read.argtypes = [C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -75,3 +78,21 @@ def check(rc: int, what: str) -> None:
     if rc != TSPLAT_OK:
         msg = lib().tsplat_last_error().decode()
         raise RuntimeError(f"{what} failed (code {rc}): {msg}")
+
+
+STAGES = ("zero", "preprocess", "bin_emit", "sort", "ranges_gather", "render_forward", "zero_bwd",
+          "render_backward", "preprocess_backward")
+
+
+def profile_enable(on: bool) -> None:
+    check(lib().tsplat_profile_enable(1 if on else 0), "tsplat_profile_enable")
+
+
+def profile_read() -> dict:
+    """Per-stage milliseconds averaged over the recorded calls (synchronises on their events)."""
+    buf = (C.c_float * (len(STAGES) + 1))()
+    check(lib().tsplat_profile_read(buf, len(STAGES) + 1), "tsplat_profile_read")
+    calls = int(buf[len(STAGES)])
+    out = {k: (float(buf[i]) / calls if calls else 0.0) for i, k in enumerate(STAGES)}
+    out["calls"] = calls
+    return out

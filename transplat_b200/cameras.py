@@ -14,9 +14,16 @@ O_VIEW, O_PROJ, O_CAMPOS, O_TANX, O_TANY, O_BG, O_MSCALE, O_CSCALE, O_DROW, O_NE
     0, 16, 32, 35, 36, 37, 40, 41, 42, 46, 47)
 
 
+def _inverse(m: Tensor) -> Tensor:
+    """Same LU kernels and values as Tensor.inverse() (what the reference calls,
+    cuda_splatting.py:95, projection.py:234) without its error check, which reads a flag back to
+    the host and so synchronises the device on every call."""
+    return torch.linalg.inv_ex(m)[0]
+
+
 def get_fov(intrinsics: Tensor) -> Tensor:
     """src/geometry/projection.py:233-247 (angle between the rays through the edge midpoints)."""
-    intrinsics_inv = intrinsics.inverse()
+    intrinsics_inv = _inverse(intrinsics)
 
     def process_vector(vector):
         vector = torch.tensor(vector, dtype=torch.float32, device=intrinsics.device)
@@ -60,7 +67,7 @@ def pack_cameras(extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tens
     render_depth_cuda (cuda_splatting.py:388-391)."""
     n = extrinsics.shape[0]
     dev = extrinsics.device
-    inv_unscaled = extrinsics.inverse()  # render_depth_cuda uses the unscaled inverse (:389)
+    inv_unscaled = _inverse(extrinsics)  # render_depth_cuda uses the unscaled inverse (:389)
     near_u, far_u = near, far
     if scale_invariant:
         scale = 1 / near
@@ -74,7 +81,7 @@ def pack_cameras(extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tens
     tan_fov_x = (0.5 * fov_x).tan()
     tan_fov_y = (0.5 * fov_y).tan()
     projection_matrix = get_projection_matrix(near, far, fov_x, fov_y).transpose(1, 2)
-    view_matrix = extrinsics.inverse().transpose(1, 2)
+    view_matrix = _inverse(extrinsics).transpose(1, 2)
     full_projection = view_matrix @ projection_matrix
 
     cams = torch.zeros((n, CAM_FLOATS), dtype=torch.float32, device=dev)

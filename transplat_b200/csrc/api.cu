@@ -130,6 +130,34 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   return w;
 }
 
+// ---- optional per-stage timing (cudaEvents on the caller's stream; off by default) ----
+enum Stage { kStZero = 0, kStPre, kStBin, kStSort, kStRanges, kStRender, kStZeroB, kStRenderB, kStPreB, kStCount };
+constexpr int kProfSlots = 256;  // ring of recorded calls; a slot = one forward + its backward
+static bool g_prof = false;
+static cudaEvent_t g_ev[kProfSlots][kStCount][2];
+static bool g_ev_made = false;
+static bool g_ev_used[kProfSlots][kStCount];
+static long long g_prof_calls = 0;  // forwards seen since enable
+struct StageTimer {
+  int s, slot; cudaStream_t st; bool on;
+  StageTimer(int s_, cudaStream_t st_) : s(s_), st(st_), on(g_prof && g_prof_calls > 0) {
+    if (!on) return;
+    slot = (int)((g_prof_calls - 1) % kProfSlots);
+    cudaEventRecord(g_ev[slot][s][0], st);
+  }
+  ~StageTimer() { if (on) { cudaEventRecord(g_ev[slot][s][1], st); g_ev_used[slot][s] = true; } }
+};
+static void prof_begin_forward() {
+  if (!g_prof) return;
+  if (!g_ev_made) {
+    for (auto& sl : g_ev) for (auto& p : sl) { cudaEventCreate(&p[0]); cudaEventCreate(&p[1]); }
+    g_ev_made = true;
+  }
+  g_prof_calls++;
+  const int slot = (int)((g_prof_calls - 1) % kProfSlots);
+  for (int s = 0; s < kStCount; s++) g_ev_used[slot][s] = false;
+}
+
 static int cuda_fail(const char* what, cudaError_t e) {
   set_error("%s: %s", what, cudaGetErrorString(e));
   return TSPLAT_ECUDA;
@@ -180,15 +208,27 @@ int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_b
   if (!out_color) { set_error("out_color is NULL"); return TSPLAT_EINVAL; }
   if (p->depth_mode != TSPLAT_DEPTH_NONE && !out_depth) { set_error("depth_mode set but out_depth is NULL"); return TSPLAT_EINVAL; }
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
-  cudaError_t e = cudaMemsetAsync(static_cast<char*>(workspace) + F.zero_begin, 0, F.zero_end - F.zero_begin, st);
+  cudaError_t e;
+  prof_begin_forward();
+  {
+    StageTimer t(kStZero, st);
+    e = cudaMemsetAsync(static_cast<char*>(workspace) + F.zero_begin, 0, F.zero_end - F.zero_begin, st);
+  }
   if (e != cudaSuccess) return cuda_fail("memset(control)", e);
   if (p->G == 0) {
     // nothing to draw: background only.  num_rendered stays 0; the render kernel sees empty ranges.
   } else {
-    if ((e = launch_preprocess(*p, ws, out_radii, st)) != cudaSuccess) return cuda_fail("preprocess", e);
-    if ((e = launch_binning(*p, ws, st)) != cudaSuccess) return cuda_fail("binning", e);
+    { StageTimer t(kStPre, st); e = launch_preprocess(*p, ws, out_radii, st); }
+    if (e != cudaSuccess) return cuda_fail("preprocess", e);
+    { StageTimer t(kStBin, st); e = launch_bin_emit(*p, ws, st); }
+    if (e != cudaSuccess) return cuda_fail("bin_emit", e);
+    { StageTimer t(kStSort, st); e = launch_sort(*p, ws, st); }
+    if (e != cudaSuccess) return cuda_fail("sort", e);
+    { StageTimer t(kStRanges, st); e = launch_ranges_gather(*p, ws, st); }
+    if (e != cudaSuccess) return cuda_fail("ranges_gather", e);
   }
-  if ((e = launch_render_forward(*p, ws, out_color, out_depth, st)) != cudaSuccess) return cuda_fail("render_forward", e);
+  { StageTimer t(kStRender, st); e = launch_render_forward(*p, ws, out_color, out_depth, st); }
+  if (e != cudaSuccess) return cuda_fail("render_forward", e);
   return TSPLAT_OK;
 }
 
@@ -204,11 +244,16 @@ int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_
   if (p->G == 0) return TSPLAT_OK;
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   const uint64_t NG = (uint64_t)p->B * p->V * p->G;
-  cudaError_t e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * NG, st);
+  cudaError_t e;
+  { StageTimer t(kStZeroB, st); e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * NG, st); }
   if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
-  if ((e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, st)) != cudaSuccess) return cuda_fail("render_backward", e);
-  if ((e = launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D, st)) != cudaSuccess)
-    return cuda_fail("preprocess_backward", e);
+  { StageTimer t(kStRenderB, st); e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, st); }
+  if (e != cudaSuccess) return cuda_fail("render_backward", e);
+  {
+    StageTimer t(kStPreB, st);
+    e = launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D, st);
+  }
+  if (e != cudaSuccess) return cuda_fail("preprocess_backward", e);
   return TSPLAT_OK;
 }
 
@@ -218,6 +263,31 @@ int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix, 
   if (G < 0 || !means || !viewmatrix || !present) { set_error("bad mark_visible arguments"); return TSPLAT_EINVAL; }
   cudaError_t e = launch_mark_visible(G, means, viewmatrix, present, static_cast<cudaStream_t>(cuda_stream));
   if (e != cudaSuccess) return cuda_fail("mark_visible", e);
+  return TSPLAT_OK;
+}
+
+int tsplat_profile_enable(int on) {
+  g_prof = on != 0;
+  g_prof_calls = 0;
+  memset(g_ev_used, 0, sizeof(g_ev_used));
+  return TSPLAT_OK;
+}
+
+int tsplat_profile_read(float* ms_host, int n) {
+  if (!ms_host || n < TSPLAT_NUM_STAGES + 1) { set_error("profile_read needs room for %d floats", TSPLAT_NUM_STAGES + 1); return TSPLAT_EINVAL; }
+  for (int s = 0; s <= kStCount; s++) ms_host[s] = 0.0f;
+  const long long calls = g_prof_calls < kProfSlots ? g_prof_calls : kProfSlots;
+  ms_host[kStCount] = (float)calls;
+  if (!g_ev_made) return TSPLAT_OK;
+  for (int slot = 0; slot < calls; slot++)
+    for (int s = 0; s < kStCount; s++) {
+      if (!g_ev_used[slot][s]) continue;
+      cudaError_t e = cudaEventSynchronize(g_ev[slot][s][1]);
+      if (e != cudaSuccess) return cuda_fail("profile_read", e);
+      float ms = 0.0f;
+      cudaEventElapsedTime(&ms, g_ev[slot][s][0], g_ev[slot][s][1]);
+      ms_host[s] += ms;
+    }
   return TSPLAT_OK;
 }
 

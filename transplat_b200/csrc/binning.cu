@@ -331,16 +331,22 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
   }
 }
 
-cudaError_t launch_binning(const TsplatProblem& p, const Workspace& ws, cudaStream_t st) {
+cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st) {
   const int total = ws.N * p.G;
   bin_emit_kernel<<<ws.num_scan_tiles, kScanThreads, 0, st>>>(ws, p.G, total);
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  return cudaGetLastError();
+}
+
+cudaError_t launch_sort(const TsplatProblem&, const Workspace& ws, cudaStream_t st) {
   for (int pass = 0; pass < ws.sort_passes; pass++) {
     onesweep_pass_kernel<<<ws.num_sort_tiles, kSortThreads, 0, st>>>(ws, pass);
-    e = cudaGetLastError();
+    cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return e;
   }
+  return cudaSuccess;
+}
+
+cudaError_t launch_ranges_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st) {
   ranges_gather_kernel<<<148 * 8, 256, 0, st>>>(ws, p.G);
   return cudaGetLastError();
 }

@@ -77,7 +77,9 @@ void set_error(const char* fmt, ...);
 
 // stage launchers (each only enqueues on `st`)
 cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, cudaStream_t st);
-cudaError_t launch_binning(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_sort(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_ranges_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color,
                                   float* out_depth, cudaStream_t st);
 cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,
