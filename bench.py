@@ -1,0 +1,384 @@
+"""bench.py — fwd+bwd views/sec of the render path at BASELINE config C2
+(RE10K training render step: 131072 Gaussians, 4 target views, 256x256, colour+depth).
+
+  python bench.py --gpus N --steps K --warmup W            # our arm (sm_100a library)
+  python bench.py --impl reference --gpus N --steps K ...  # CPU arm: the oracle port on host cores
+
+A "step" = one pass of the hot path over one batch: DecoderSplattingCUDA.forward(depth_mode="depth")
++ backward for 1 scene x 4 views per rank.  Ranks render independent scenes (scene sharding, no
+collective) => weak scaling.  One JSON line is printed by rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+G_CTX, HW, VIEWS = 2, 256, 4          # C2: 2 context views of 256x256 -> 131072 Gaussians; 4 target views
+N_SCENES = 4                           # distinct resident scenes cycled through (4 x 46 MB of inputs)
+METRIC = "fwd+bwd views/sec (256x256, 131072 Gaussians/scene)"
+UNIT = "views/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks: sampled DURING the timed region (NVML; nvidia-smi fallback)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    def __init__(self, index: int):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+                 0x80: "hw_power_brake_slowdown"}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                try:
+                    r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                except Exception:
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in names.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.05)
+
+    def start(self):
+        if self.nv is not None:
+            self._t = threading.Thread(target=self._loop, daemon=True)
+            self._t.start()
+
+    def stop(self) -> dict:
+        self._stop.set()
+        if self._t is not None:
+            self._t.join()
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------
+def make_inputs(rank: int, n_scenes: int):
+    import torch
+    from transplat_b200.synthetic import make_scene, upstream_grads
+    scenes = [make_scene(n_ctx=G_CTX, h=HW, w=HW, n_views=VIEWS, seed=1236 + 100 * rank + i) for i in range(n_scenes)]
+    target, dLd = upstream_grads(VIEWS, HW, HW, seed=99 + rank)
+    return scenes, target, dLd
+
+
+def bytes_per_view(G: int, D_per_view: float, P: int, T: int) -> float:
+    """B_view = 1232 G + 260 D + 48 P + 8 T (fwd+bwd, colour+depth fused, fp32)."""
+    return 1232.0 * G + 260.0 * D_per_view + 48.0 * P + 8.0 * T
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from transplat_b200 import _lib
+    from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+
+    rank, local_rank, world = dist_env()
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py (our arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.lib()  # fail loudly if libtsplat.so is missing
+
+    scenes, target_h, dLd_h = make_inputs(rank, N_SCENES)
+    G = scenes[0].means.shape[0]
+    P, T = HW * HW, (HW // 16) ** 2
+    decoder = DecoderSplattingCUDA().to(dev)
+    numel = float(VIEWS * 3 * HW * HW)
+
+    def to_dev(sc):
+        leaf = lambda t: t.to(dev).requires_grad_(True)
+        return dict(means=leaf(sc.means[None]), cov=leaf(sc.covariances[None]), sh=leaf(sc.harmonics[None]),
+                    op=leaf(sc.opacities[None]), ext=sc.extrinsics[None].to(dev), intr=sc.intrinsics[None].to(dev),
+                    near=sc.near[None].to(dev), far=sc.far[None].to(dev))
+
+    dev_scenes = [to_dev(s) for s in scenes]
+    target = target_h[None].to(dev)
+    dLd = dLd_h[None].to(dev)
+
+    def step(s):
+        g = Gaussians(s["means"], s["cov"], s["sh"], s["op"])
+        out = decoder.forward(g, s["ext"], s["intr"], s["near"], s["far"], (HW, HW), depth_mode="depth")
+        dLc = (out.color - target) * (2.0 / numel)  # MSE gradient (loss_mse.py:30-31)
+        return out, torch.autograd.grad([out.color, out.depth], [s["means"], s["cov"], s["sh"], s["op"]], [dLc, dLd])
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(dev_scenes[i % N_SCENES])
+    barrier()
+
+    # ---- timed region: device-resident inputs, one CUDA-event pair per step, L2 flushed between steps
+    _lib.profile_enable(True)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    barrier()
+    t_wall = time.perf_counter()
+    for i in range(args.steps):
+        flush.zero_()
+        ev[i][0].record()
+        step(dev_scenes[i % N_SCENES])
+        ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    clocks = sampler.stop()
+    stages = _lib.profile_read()
+    _lib.profile_enable(False)
+    ms_total = sum(a.elapsed_time(b) for a, b in ev)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_per_step = ms_total / args.steps
+    value = world * VIEWS / (ms_per_step * 1e-3)
+
+    # measured pair count D (per call = all 4 views) of the last step
+    from transplat_b200.rasterize import _capacity
+    D_call = None
+    for key in list(_capacity.pending):
+        st = _capacity.poll(key, wait=True)
+        if st is not None:
+            D_call = int(st.num_rendered)
+
+    # ---- end to end through the public API with HOST buffers (H2D + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (SURVEY 8d algorithmic bytes; one launch covers VIEWS views)
+    Dv = (D_call or 3 * G * VIEWS) / VIEWS
+    alg = {"preprocess": 392.0 * G, "bin_emit": 28.0 * G + 12.0 * Dv, "sort": 152.0 * Dv,
+           "ranges_gather": 8.0 * Dv + 8.0 * T, "render_forward": 44.0 * Dv + 24.0 * P,
+           "render_backward": 44.0 * Dv + 24.0 * P + 40.0 * G, "preprocess_backward": 772.0 * G}
+    kern = {k: stages[k] for k in alg}
+    top = max(kern, key=kern.get)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    top_bytes = alg[top] * VIEWS
+    achieved = top_bytes / (kern[top] * 1e-3) / 1e9 if kern[top] > 0 else 0.0
+    step_bytes = bytes_per_view(G, Dv, P, T) * VIEWS
+    traffic = load_traffic(top)
+    line = {
+        "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "C2: RE10K training render step, 1 scene x 4 target views per GPU, 256x256, "
+                               "131072 Gaussians (SH degree 4), colour+depth fwd+bwd",
+                   "gaussians": G, "views_per_step_per_gpu": VIEWS, "pairs_per_view": round(Dv),
+                   "parallelism": f"scene-sharded x{world} (no collective)",
+                   "l2": "256 MiB buffer zeroed between timed steps (outside the event pairs); "
+                         f"{N_SCENES} scenes cycled",
+                   "api": "DecoderSplattingCUDA.forward(depth_mode='depth') + torch.autograd.grad"},
+        "clocks": clocks,
+        "e2e": e2e,
+        "gpu_launches": args.steps * (6 + sort_passes(VIEWS, T)),
+        "roofline": {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+                     "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                     "algorithmic_bytes_per_launch": round(top_bytes), "kernel_ms": round(kern[top], 4),
+                     "stage_ms": {k: round(v, 4) for k, v in stages.items()},
+                     "step": {"algorithmic_bytes": round(step_bytes),
+                              "achieved": round(step_bytes / (ms_per_step * 1e-3) / 1e9, 1),
+                              "frac": round(step_bytes / (ms_per_step * 1e-3) / 1e9 / peak, 4)}},
+        "host_wall_ms_per_step": round(t_wall * 1e3 / args.steps, 4),
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(scenes[0], target_h, dLd_h, budget_s=12.0)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def sort_passes(n_views: int, T: int) -> int:
+    bits = 32 + max(1, (n_views * T - 1).bit_length())
+    return (bits + 7) // 8
+
+
+def load_traffic(kernel: str):
+    """dram bytes per launch of the dominant kernel from the committed `ncu --set full` summary."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return d.get(kernel)
+    except Exception:
+        return None
+
+
+def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
+    """Same step through the public API, but every step starts from PINNED HOST buffers and ends with
+    the results (colour, depth, the four gradients) back in pinned host memory."""
+    import torch
+    import torch.distributed as dist
+    from transplat_b200.decoder import Gaussians
+
+    pin = lambda t: t.contiguous().pin_memory()
+    host = [dict(means=pin(s.means[None]), cov=pin(s.covariances[None]), sh=pin(s.harmonics[None]),
+                 op=pin(s.opacities[None]), ext=pin(s.extrinsics[None]), intr=pin(s.intrinsics[None]),
+                 near=pin(s.near[None]), far=pin(s.far[None])) for s in scenes]
+    tgt_h, dLd_hp = pin(target_h[None]), pin(dLd_h[None])
+    G = scenes[0].means.shape[0]
+    out_h = dict(color=torch.empty((1, VIEWS, 3, HW, HW)).pin_memory(), depth=torch.empty((1, VIEWS, HW, HW)).pin_memory(),
+                 g_means=torch.empty((1, G, 3)).pin_memory(), g_cov=torch.empty((1, G, 3, 3)).pin_memory(),
+                 g_sh=torch.empty((1, G, 3, 25)).pin_memory(), g_op=torch.empty((1, G)).pin_memory())
+    numel = float(VIEWS * 3 * HW * HW)
+    h2d = sum(t.numel() * 4 for t in host[0].values()) + tgt_h.numel() * 4 + dLd_hp.numel() * 4
+    d2h = sum(t.numel() * 4 for t in out_h.values())
+
+    def step(h):
+        d = {k: v.to(dev, non_blocking=True) for k, v in h.items()}
+        target, dLd = tgt_h.to(dev, non_blocking=True), dLd_hp.to(dev, non_blocking=True)
+        leaves = [d[k].requires_grad_(True) for k in ("means", "cov", "sh", "op")]
+        out = decoder.forward(Gaussians(*leaves), d["ext"], d["intr"], d["near"], d["far"], (HW, HW), depth_mode="depth")
+        dLc = (out.color - target) * (2.0 / numel)
+        grads = torch.autograd.grad([out.color, out.depth], leaves, [dLc, dLd])
+        out_h["color"].copy_(out.color.detach(), non_blocking=True)
+        out_h["depth"].copy_(out.depth.detach(), non_blocking=True)
+        for k, g in zip(("g_means", "g_cov", "g_sh", "g_op"), grads):
+            out_h[k].copy_(g, non_blocking=True)
+
+    steps = max(5, min(args.steps, 30))
+    for i in range(3):
+        step(host[i % N_SCENES])
+    barrier()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    for i in range(steps):
+        flush.zero_()
+        ev[i][0].record()
+        step(host[i % N_SCENES])
+        ev[i][1].record()
+    barrier()
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    ms /= steps
+    return {"value": round(world * VIEWS / (ms * 1e-3), 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+            "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms, 4), "steps": steps}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port (oracle/tsplat_oracle.c, OpenMP) on the host cores.  The reference's own
+# arithmetic lives in an external extension whose source is absent, so "reference" here
+# is the port, kind "port".
+# ------------------------------------------------------------------------------------------------
+def oracle_step(scene, target, dLd):
+    """One C2 step on the CPU: 4 views colour+depth forward, MSE gradient, backward summed over views."""
+    import numpy as np
+    import torch
+    import oracle
+    from transplat_b200.cameras import pack_cameras
+
+    G = scene.means.shape[0]
+    cams = pack_cameras(scene.extrinsics, scene.intrinsics, scene.near, scene.far, torch.zeros(VIEWS, 3)).numpy()
+    sc = oracle.Scene(scene.means.numpy(), scene.covariances.numpy(), scene.harmonics.numpy(), scene.opacities.numpy(),
+                      4, oracle.SH_G3M, oracle.COV_FULL9)
+    acc = oracle.GradAccum(sc)
+    numel = float(VIEWS * 3 * HW * HW)
+    tgt, dd = target.numpy(), dLd.numpy()
+    for v in range(VIEWS):
+        st = oracle.forward(sc, cams[v], HW, HW, depth_mode="depth")
+        dLc = (st.color - tgt[v]) * np.float32(2.0 / numel)
+        oracle.backward(sc, cams[v], st, dLc, dd[v], acc=acc, depth_mode="depth")
+    return acc
+
+
+def cpu_baseline(scene, target, dLd, budget_s: float):
+    import oracle
+    oracle_step(scene, target, dLd)  # warm-up (builds the library, pages it in)
+    t0, n = time.perf_counter(), 0
+    while n < 1 or (time.perf_counter() - t0 < budget_s and n < 16):
+        oracle_step(scene, target, dLd)
+        n += 1
+    dt = time.perf_counter() - t0
+    return {"value": round(n * VIEWS / dt, 3), "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+            "sample": f"{n} full C2 steps (1 scene x {VIEWS} views fwd+bwd, colour+depth) of the same workload, "
+                      f"oracle/tsplat_oracle.c with OpenMP, {dt:.1f} s"}
+
+
+def run_reference(args):
+    rank, _, world = dist_env()
+    if rank != 0:
+        return
+    import oracle
+    scenes, target, dLd = make_inputs(0, 1)
+    for _ in range(max(1, min(args.warmup, 3))):
+        oracle_step(scenes[0], target, dLd)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle_step(scenes[0], target, dLd)
+    dt = time.perf_counter() - t0
+    value = args.steps * VIEWS / dt
+    line = {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": round(dt * 1e3 / args.steps, 3),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "C2: RE10K training render step, 1 scene x 4 target views, 256x256, 131072 Gaussians "
+                                   "(SH degree 4), colour+depth fwd+bwd", "gaussians": int(scenes[0].means.shape[0]),
+                       "note": "CPU port of the rasterizer (the reference's own CUDA extension is an unpinned external "
+                               "dependency whose source is absent); rank 0 only, host cores"},
+            "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+                             "sample": f"{args.steps} full C2 steps, {dt:.1f} s"},
+            "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

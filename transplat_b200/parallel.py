@@ -1,0 +1,84 @@
+"""Multi-GPU plumbing for the render path: one process per GPU, torch.distributed.
+
+* scene sharding — scenes are independent: scene s -> rank s mod N, no data-path collective
+  (the pattern of the reference's Lightning DDP over scenes, src/main.py:117-129).
+* view sharding — one scene's target views split over ranks (view j -> rank j mod N), Gaussians
+  replicated; forward needs no communication; backward sums the per-Gaussian gradients
+  (means 3 + covariance 9 + SH 75 + opacity 1 floats per Gaussian) with ONE all-reduce over a
+  single flat slab.  This is the only collective on the path.
+"""
+from __future__ import annotations
+
+from typing import Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .decoder import DecoderOutput, Gaussians
+
+
+def shard_indices(n: int, rank: int, world: int) -> list:
+    """Round-robin ownership: item i belongs to rank i mod world."""
+    return list(range(rank, n, world))
+
+
+def shard_counts(n: int, world: int) -> list:
+    return [len(range(r, n, world)) for r in range(world)]
+
+
+class _SumGradsAcrossRanks(torch.autograd.Function):
+    """Identity in forward; in backward the gradients of all tensors are packed into one flat
+    buffer, summed over the group with a single all-reduce, and unpacked."""
+
+    @staticmethod
+    def forward(ctx, group, *tensors):
+        ctx.group = group
+        return tuple(t.view_as(t) for t in tensors)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        shapes = [g.shape for g in grads]
+        sizes = [g.numel() for g in grads]
+        slab = torch.empty(sum(sizes), dtype=grads[0].dtype, device=grads[0].device)
+        off = 0
+        for g, n in zip(grads, sizes):
+            slab[off:off + n].copy_(g.reshape(-1))
+            off += n
+        dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=ctx.group)
+        out, off = [], 0
+        for shp, n in zip(shapes, sizes):
+            out.append(slab[off:off + n].view(shp))
+            off += n
+        return (None, *out)
+
+
+def replicate_with_summed_grads(gaussians: Gaussians, group=None) -> Gaussians:
+    """Gaussians replicated on every rank whose gradients are all-reduced (sum) in backward."""
+    m, c, h, o = _SumGradsAcrossRanks.apply(group, gaussians.means, gaussians.covariances, gaussians.harmonics,
+                                            gaussians.opacities)
+    return Gaussians(m, c, h, o)
+
+
+def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
+                         depth_mode: Optional[str] = None, group=None) -> tuple:
+    """Each rank renders views rank, rank+N, ... of every scene in the batch.  Returns
+    (DecoderOutput for the local views, list of the global view indices rendered here).  Backward
+    through the output all-reduces the per-Gaussian gradients once."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    v = extrinsics.shape[1]
+    mine = shard_indices(v, rank, world)
+    if world > 1:
+        gaussians = replicate_with_summed_grads(gaussians, group)
+    if not mine:
+        # a rank without views would skip backward and leave the others waiting in the all-reduce
+        raise ValueError(f"view sharding needs at least one view per rank (views={v}, ranks={world})")
+    idx = torch.tensor(mine, device=extrinsics.device)
+    out = decoder.forward(gaussians, extrinsics[:, idx], intrinsics[:, idx], near[:, idx], far[:, idx], image_shape,
+                          depth_mode=depth_mode)
+    return out, mine
+
+
+def forward_scene_sharded(decoder, scenes: Sequence, rank: int, world: int, render_one):
+    """Scene sharding: `render_one(decoder, scene)` is called for the scenes this rank owns."""
+    return {s: render_one(decoder, scenes[s]) for s in shard_indices(len(scenes), rank, world)}
