@@ -162,6 +162,19 @@ int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_
 int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix,
                         const float* projmatrix, uint8_t* present, void* cuda_stream);
 
+/* Device-side camera preparation for the batched decoder path: fills cams[N]
+ * from what DecoderSplattingCUDA.forward receives, in one launch and with no host synchronisation.
+ * Replaces the host arithmetic of render_cuda / render_depth_cuda:
+ *   cuda_splatting.py:73-80 (scale invariance), :89-91 (get_fov, projection.py:233-247, tan),
+ *   :93-96 (get_projection_matrix :26-53, extrinsics.inverse(), view @ projection),
+ *   :111-112 (the two .item() host reads per view), :388-391 (unscaled inverse row for depth).
+ *   extrinsics [N,4,4] camera-to-world (row-major), intrinsics [N,3,3] normalised, near/far [N],
+ *   bg [N,3] with bg_stride = 3, or one [3] colour for every camera with bg_stride = 0. */
+int tsplat_pack_cameras(int32_t N, const float* extrinsics, const float* intrinsics,
+                        const float* near_plane, const float* far_plane, const float* bg,
+                        int32_t bg_stride, int32_t scale_invariant, TsplatCamera* cams,
+                        void* cuda_stream);
+
 /* Copies the status block to pinned/pageable host memory asynchronously on the stream. */
 int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream);
 

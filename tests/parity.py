@@ -76,6 +76,7 @@ def compare_forward(ins: dict, color, depth, states, cfg: RenderConfig) -> dict:
             rep["depth_max_abs"] = max(rep["depth_max_abs"], float(np.abs(depth[n] - st.depth).max()))
         off += D
         D_total += D
+    rep["pixels"] = int(color.shape[0] * color.shape[-2] * color.shape[-1])
     rep["num_rendered_gpu"] = cpu["num_rendered"]
     rep["num_rendered_oracle"] = D_total
     return rep

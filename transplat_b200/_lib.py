@@ -16,7 +16,7 @@ COV_TRIU6, COV_FULL9 = 0, 1
 DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
-           "tsplat_backward", "tsplat_mark_visible", "tsplat_status_read", "tsplat_profile_enable",
+           "tsplat_backward", "tsplat_mark_visible", "tsplat_pack_cameras", "tsplat_status_read", "tsplat_profile_enable",
            "tsplat_profile_read")
 
 
@@ -67,6 +67,8 @@ def lib():
                                       C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                       C.c_void_p, C.c_void_p, C.c_void_p]
         L.tsplat_mark_visible.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_pack_cameras.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         L.tsplat_status_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.tsplat_profile_enable.argtypes = [C.c_int]
         L.tsplat_profile_read.argtypes = [C.c_void_p, C.c_int]

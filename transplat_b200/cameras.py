@@ -99,6 +99,39 @@ def pack_cameras(extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tens
     return cams
 
 
+def pack_cameras_device(extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
+                        background_color: Tensor, scale_invariant: bool = True) -> Tensor:
+    """Same contract as :func:`pack_cameras`, computed by ONE kernel of libtsplat.so
+    (tsplat_pack_cameras, csrc/cameras.cu) on the current stream: no torch op chain (the torch
+    restatement above is ~100 tiny launches per call), no host synchronisation.
+    ``background_color`` is [3] (shared) or [N,3]."""
+    import ctypes as C
+
+    from . import _lib
+
+    if not extrinsics.is_cuda:
+        raise RuntimeError("transplat_b200 renders on a CUDA device only (no CPU fallback): cameras must be CUDA tensors")
+    n = extrinsics.shape[0]
+    dev = extrinsics.device
+    f32 = lambda t: t.to(dtype=torch.float32).contiguous()
+    extrinsics, intrinsics, near, far, bg = (f32(t) for t in (extrinsics, intrinsics, near, far, background_color))
+    if tuple(extrinsics.shape) != (n, 4, 4) or tuple(intrinsics.shape) != (n, 3, 3) or near.numel() != n or far.numel() != n:
+        raise RuntimeError("pack_cameras_device: extrinsics [N,4,4], intrinsics [N,3,3], near/far [N] expected")
+    if bg.numel() == 3:
+        stride = 0
+    elif tuple(bg.shape) == (n, 3):
+        stride = 3
+    else:
+        raise RuntimeError("background_color must be [3] or [N,3]")
+    cams = torch.empty((n, CAM_FLOATS), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _lib.check(_lib.lib().tsplat_pack_cameras(n, extrinsics.data_ptr(), intrinsics.data_ptr(), near.data_ptr(),
+                                                  far.data_ptr(), bg.data_ptr(), stride, 1 if scale_invariant else 0,
+                                                  cams.data_ptr(), C.c_void_p(stream)), "tsplat_pack_cameras")
+    return cams
+
+
 def pack_camera_from_settings(viewmatrix: Tensor, projmatrix: Tensor, campos: Tensor, tanfovx,
                               tanfovy, bg: Tensor) -> Tensor:
     """Level 1: one record from the fields of GaussianRasterizationSettings

@@ -266,6 +266,20 @@ int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix, 
   return TSPLAT_OK;
 }
 
+int tsplat_pack_cameras(int32_t N, const float* extrinsics, const float* intrinsics, const float* near_plane,
+                        const float* far_plane, const float* bg, int32_t bg_stride, int32_t scale_invariant,
+                        TsplatCamera* cams, void* cuda_stream) {
+  if (N < 0 || !extrinsics || !intrinsics || !near_plane || !far_plane || !bg || !cams ||
+      (bg_stride != 0 && bg_stride != 3)) {
+    set_error("bad pack_cameras arguments");
+    return TSPLAT_EINVAL;
+  }
+  cudaError_t e = launch_pack_cameras(N, extrinsics, intrinsics, near_plane, far_plane, bg, bg_stride,
+                                      scale_invariant, cams, static_cast<cudaStream_t>(cuda_stream));
+  if (e != cudaSuccess) return cuda_fail("pack_cameras", e);
+  return TSPLAT_OK;
+}
+
 int tsplat_profile_enable(int on) {
   g_prof = on != 0;
   g_prof_calls = 0;

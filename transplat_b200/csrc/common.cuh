@@ -87,6 +87,9 @@ cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, 
 cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& ws, float* dL_dmeans,
                                        float* dL_dcov, float* dL_dsh, float* dL_dopacity,
                                        float* dL_dmeans2D, cudaStream_t st);
+cudaError_t launch_pack_cameras(int N, const float* extrinsics, const float* intrinsics, const float* near_,
+                                const float* far_, const float* bg, int bg_stride, int scale_invariant,
+                                TsplatCamera* out, cudaStream_t st);
 cudaError_t launch_mark_visible(int G, const float* means, const float* view, uint8_t* present,
                                 cudaStream_t st);
 

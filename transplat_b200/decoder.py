@@ -25,7 +25,7 @@ import torch
 from torch import Tensor, nn
 
 from ._lib import COV_FULL9, DEPTH_MODES, SH_G3M
-from .cameras import pack_cameras
+from .cameras import pack_cameras_device
 from .rasterize import RenderConfig, rasterize
 
 DepthRenderingMode = Literal["depth", "log", "disparity", "relative_disparity"]
@@ -68,9 +68,9 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
         raise ValueError(f"unknown depth_mode {depth_mode!r}")
     d_sh = gaussians.harmonics.shape[-1]
     degree = isqrt(d_sh) - 1
-    bg = background_color if background_color.dim() == 2 else background_color.expand(b * v, 3)
-    cams = pack_cameras(extrinsics.reshape(b * v, 4, 4), intrinsics.reshape(b * v, 3, 3),
-                        near.reshape(b * v), far.reshape(b * v), bg, scale_invariant=scale_invariant)
+    cams = pack_cameras_device(extrinsics.reshape(b * v, 4, 4), intrinsics.reshape(b * v, 3, 3),
+                               near.reshape(b * v), far.reshape(b * v), background_color,
+                               scale_invariant=scale_invariant)
     cfg = RenderConfig(H=h, W=w, V=v, sh_degree=degree, sh_layout=SH_G3M, cov_layout=COV_FULL9,
                        depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check)
     color, depth, radii = rasterize(gaussians.means, gaussians.covariances, gaussians.harmonics,

@@ -33,6 +33,24 @@ class _Capacity:
     def __init__(self):
         self.cap = {}
         self.pending = {}
+        self.unchecked = []  # (host, event, d_cap) of backward calls launched before their status arrived
+
+    def check_unchecked(self):
+        """Raise for an earlier call whose overflow flag could not be read without stalling."""
+        keep = []
+        bad = None
+        for host, event, d_cap in self.unchecked:
+            if not event.query():
+                keep.append((host, event, d_cap))
+                continue
+            st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
+            if st.overflow:
+                bad = (st.num_rendered, d_cap)
+        self.unchecked = keep
+        if bad is not None:
+            raise OverflowError_(
+                f"pair list overflow in an EARLIER render call: D={bad[0]} > d_cap={bad[1]}; its images and "
+                "gradients were incomplete.  Raise TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
 
     def get(self, key, n_items):
         self.poll(key)
@@ -131,6 +149,8 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
     dev = means.device
     key = (dev.index, N, G, cfg.H, cfg.W)
     check = cfg.check or _CHECK_MODE
+    if _capacity.unchecked:
+        _capacity.check_unchecked()
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev)
         while True:
@@ -176,11 +196,19 @@ def read_status(state) -> TsplatStatus:
 def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
     L = _lib.lib()
     means, cov, sh, opacity, cams = state.tensors
-    st = read_status(state)  # the forward finished long ago: this does not stall the pipeline
-    if st.overflow:
-        raise OverflowError_(
-            f"pair list overflow in the forward pass: D={st.num_rendered} > d_cap={state.d_cap}; the rendered "
-            "images were incomplete.  Raise TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
+    if _capacity.unchecked:
+        _capacity.check_unchecked()
+    if state.event.query() or (cfg.check or _CHECK_MODE) == "sync":
+        st = read_status(state)
+        if st.overflow:
+            raise OverflowError_(
+                f"pair list overflow in the forward pass: D={st.num_rendered} > d_cap={state.d_cap}; the rendered "
+                "images were incomplete.  Raise TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
+    else:
+        # the forward is still in flight (training step: backward is issued right behind it).  Do not
+        # stall the host: enqueue the backward now (memory-safe even after an overflow) and read the flag
+        # at the next call.
+        _capacity.unchecked.append((state.status_host, state.event, state.d_cap))
     dev = means.device
     N = means.shape[0] * cfg.V
     with torch.cuda.device(dev):
