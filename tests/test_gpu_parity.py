@@ -106,7 +106,7 @@ def test_golden_level1_rasterizer_loop():
                                           1.0, view[i], full[i], isqrt(25) - 1, ext[i, :3, 3], False, False)
         img, radii = GaussianRasterizer(s)(means3D=means[i], means2D=m2d, shs=shs, colors_precomp=None,
                                            opacities=t("opacities")[..., None], cov3D_precomp=cov[i][:, row, col])
-        assert np.abs(img.cpu().numpy() - z["color"][i]).max() <= COLOR_ATOL
+        assert np.abs(img.detach().cpu().numpy() - z["color"][i]).max() <= COLOR_ATOL
         assert radii.dtype == torch.int32 and radii.shape == (means.shape[1],) and int((radii > 0).sum()) > 0
     rep = lambda k: t(k)[None].expand(V, *z[k].shape)
     color = D.render_cuda(t("extrinsics"), intr, near, far, (H, W), t("bg")[None].expand(V, 3), rep("means"), rep("cov"),

@@ -8,6 +8,8 @@
 // depth feature (4th channel) are composited in the same pass (the reference renders depth with a
 // second full pass, cuda_splatting.py:404).  Termination is voted per warp (__all_sync) and per
 // CTA (__syncthreads_count), as the reference does per CTA.
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace tsplat {
@@ -29,19 +31,46 @@ __device__ __forceinline__ void issue_batch(Smem& s, int buf, const Workspace& w
   bulk_g2s(s.r2[buf], ws.rec2 + first, bytes, &s.full[buf]);
 }
 
+// Pixel <-> thread mapping: warp w owns an 8x4 pixel block of the 16x16 tile (2 block columns x 4
+// block rows), lane l the pixel (l & 7, l >> 3) of it.  A compact block makes the per-warp culling
+// below effective (the mapping itself is invisible in the results).
+__device__ __forceinline__ void pixel_of_thread(int tid, int& bx, int& by, int& lx, int& ly) {
+  const int warp = tid >> 5, lane = tid & 31;
+  bx = (warp & 1) * 8; by = (warp >> 1) * 4;
+  lx = lane & 7; ly = lane >> 3;
+}
+
+// Per-warp culling of one staged batch: bit l of mask[i] is set iff entry 32*i + l can touch the
+// warp's block [X0, X0+7] x [Y0, Y0+3] according to the conservative extents packed in rec2.w
+// (cull_extent, binning.cu).  One entry per lane, 8 rounds per 256-entry batch.
+__device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0, const float4* __restrict__ r2,
+                                                   int j, bool in_range, float X0, float Y0) {
+  bool hit = false;
+  if (in_range) {
+    const float2 c = *reinterpret_cast<const float2*>(&r0[j]);
+    const unsigned int e = __float_as_uint(r2[j].w);
+    const float hx = __half2float(__ushort_as_half((unsigned short)(e & 0xffffu)));
+    const float hy = __half2float(__ushort_as_half((unsigned short)(e >> 16)));
+    hit = (c.x + hx >= X0) && (c.x - hx <= X0 + 7.0f) && (c.y + hy >= Y0) && (c.y - hy <= Y0 + 3.0f);
+  }
+  return __ballot_sync(0xffffffffu, hit);
+}
+
 template <int CH>
 __global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, int H, int W,
                                                                   const TsplatCamera* __restrict__ cams,
                                                                   float* __restrict__ out_color,
                                                                   float* __restrict__ out_depth) {
   __shared__ __align__(128) RenderSmem s;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31;
   const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
   const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
-  // warp w covers rows 2w, 2w+1 of the tile: 16 consecutive pixels per half-warp
-  const int px = tx * kTile + (tid & 15), py = ty * kTile + (tid >> 4);
+  int bx, by, lx, ly;
+  pixel_of_thread(tid, bx, by, lx, ly);
+  const int px = tx * kTile + bx + lx, py = ty * kTile + by + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
+  const float X0 = (float)(tx * kTile + bx), Y0 = (float)(ty * kTile + by);
   const uint2 range = ws.ranges[blockIdx.x];
   const int total = (int)(range.y - range.x);
   const int nb = (total + kBatch - 1) / kBatch;
@@ -58,7 +87,7 @@ __global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, 
   float C[CH];
 #pragma unroll
   for (int ch = 0; ch < CH; ch++) C[ch] = 0.0f;
-  unsigned int contributor = 0, last_contributor = 0;
+  unsigned int last_contributor = 0;
   bool done = !inside;
   int consumed = 0;  // batches whose barrier has been waited on
 
@@ -72,27 +101,41 @@ __global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, 
     const int buf = b & 1;
     mbar_wait(&s.full[buf], (b >> 1) & 1);
     consumed = b + 1;
+    if (__all_sync(0xffffffffu, done)) continue;  // this warp has finished; keep voting with the CTA
     const int cnt = min(kBatch, total - b * kBatch);
-    for (int j = 0; j < cnt; j++) {
-      if ((j & 7) == 0 && __all_sync(0xffffffffu, done)) break;  // warp-level early out
-      contributor++;
-      const float4 a0 = s.r0[buf][j];
-      const float4 a1 = s.r1[buf][j];
-      const float dx = a0.x - pxf, dy = a0.y - pyf;
-      const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
-      if (done || power > 0.0f) continue;
-      const float alpha = fminf(0.99f, a1.y * __expf(power));
-      if (alpha < 1.0f / 255.0f) continue;
-      const float test_T = T * (1.0f - alpha);
-      if (test_T < 0.0001f) { done = true; continue; }
-      const float4 a2 = s.r2[buf][j];
-      const float w = alpha * T;
-      C[0] += a1.z * w;
-      C[1] += a1.w * w;
-      C[2] += a2.x * w;
-      if (CH == 4) C[3] += a2.y * w;
-      T = test_T;
-      last_contributor = contributor;
+    const float4* __restrict__ r0 = s.r0[buf];
+    const float4* __restrict__ r1 = s.r1[buf];
+    const float4* __restrict__ r2 = s.r2[buf];
+    unsigned int mask[kBatch / 32];
+#pragma unroll
+    for (int i = 0; i < kBatch / 32; i++) mask[i] = cull_round(r0, r2, i * 32 + lane, i * 32 + lane < cnt, X0, Y0);
+    const unsigned int base = (unsigned int)(b * kBatch) + 1u;  // 1-based list position of entry 0
+#pragma unroll
+    for (int i = 0; i < kBatch / 32; i++) {
+      unsigned int m = mask[i];
+      if (m == 0u) continue;
+      if (__all_sync(0xffffffffu, done)) break;  // warp-level early out, once per 32 entries
+      while (m) {
+        const int j = i * 32 + (__ffs(m) - 1);
+        m &= m - 1u;
+        const float4 a0 = r0[j];
+        const float4 a1 = r1[j];
+        const float dx = a0.x - pxf, dy = a0.y - pyf;
+        const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+        if (done || power > 0.0f) continue;
+        const float alpha = fminf(0.99f, a1.y * __expf(power));
+        if (alpha < 1.0f / 255.0f) continue;
+        const float test_T = T * (1.0f - alpha);
+        if (test_T < 0.0001f) { done = true; continue; }
+        const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
+        const float w = alpha * T;
+        C[0] += a1.z * w;
+        C[1] += a1.w * w;
+        C[2] += a2.x * w;
+        if (CH == 4) C[3] += a2.y * w;
+        T = test_T;
+        last_contributor = base + (unsigned int)j;
+      }
     }
   }
   // never leave the CTA with a bulk copy still in flight into its shared memory
@@ -190,6 +233,11 @@ __device__ __forceinline__ int comp_of_lane(int lane) {
   return ia + 5 * h16;                 // slot in v[] (0..9)
 }
 
+// one 16-B vector reduction into global memory (sm_90+): 4 fp32 adds, one L2 operation
+__device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 template <int CH>
 __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws, int H, int W, int G,
                                                                    const TsplatCamera* __restrict__ cams,
@@ -200,9 +248,12 @@ __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws,
   const int tid = threadIdx.x, lane = tid & 31;
   const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
   const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
-  const int px = tx * kTile + (tid & 15), py = ty * kTile + (tid >> 4);
+  int bx, by, lx, ly;
+  pixel_of_thread(tid, bx, by, lx, ly);
+  const int px = tx * kTile + bx + lx, py = ty * kTile + by + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
+  const float X0 = (float)(tx * kTile + bx), Y0 = (float)(ty * kTile + by);
   const uint2 range = ws.ranges[blockIdx.x];
   const int total = (int)(range.y - range.x);
   const int nb = (total + kBatch - 1) / kBatch;
@@ -236,9 +287,13 @@ __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws,
   const float* bgp = cams[n].bg;
   // bg of the fused depth channel is 0 (render_depth_cuda passes zeros, cuda_splatting.py:410)
   const float bg_dot = __ldg(bgp) * dL_dpix[0] + __ldg(bgp + 1) * dL_dpix[1] + __ldg(bgp + 2) * dL_dpix[2];
+  const float bgT = -T_final * bg_dot;
   float last_alpha = 0.0f;
   const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
   const int my_comp = comp_of_lane(lane);
+  const bool my_red = my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9);
+  // list positions >= the warp's deepest contributor are never visited by this warp
+  const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
 
   for (int b = 0; b < nb; b++) {
     const int buf = b & 1;
@@ -246,65 +301,84 @@ __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws,
     if (tid == 0 && b + 1 < nb)  // buffer (b+1)&1 was released by the barrier that ended batch b-1
       issue_batch(s, (b + 1) & 1, ws, (unsigned)batch_lo(b + 1), (unsigned)(batch_hi(b + 1) - batch_lo(b + 1)));
     mbar_wait(&s.full[buf], (b >> 1) & 1);
-    // entries of this batch with list position >= the warp's deepest contributor are skipped whole
-    const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
-    for (int j = cnt - 1; j >= 0; j--) {
-      const int pos = lo + j - (int)range.x;  // 0-based position in the tile's list
-      if (pos >= warp_last) continue;         // warp-uniform
-      const float4 a0 = s.r0[buf][j];
-      const float4 a1 = s.r1[buf][j];
-      const float dx = a0.x - pxf, dy = a0.y - pyf;
-      const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
-      const float Gv = __expf(power);
-      const float alpha = fminf(0.99f, a1.y * Gv);
-      const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-      if (!__any_sync(0xffffffffu, valid)) continue;
-      float v[10];
+    const float4* __restrict__ r0 = s.r0[buf];
+    const float4* __restrict__ r1 = s.r1[buf];
+    const float4* __restrict__ r2 = s.r2[buf];
+    const int pos0 = lo - (int)range.x;  // 0-based list position of entry 0 of this batch
+    if (pos0 < warp_last) {
+      unsigned int mask[kBatch / 32];
 #pragma unroll
-      for (int k = 0; k < 10; k++) v[k] = 0.0f;
-      if (valid) {
-        const float4 a2 = s.r2[buf][j];
-        const float col[4] = {a1.z, a1.w, a2.x, a2.y};
-        T = T / (1.0f - alpha);
-        const float dchannel_dcolor = alpha * T;
-        float dL_dalpha = 0.0f;
-#pragma unroll
-        for (int ch = 0; ch < CH; ch++) {
-          const float c = col[ch];
-          accum_rec[ch] = last_alpha * last_color[ch] + (1.0f - last_alpha) * accum_rec[ch];
-          last_color[ch] = c;
-          dL_dalpha += (c - accum_rec[ch]) * dL_dpix[ch];
-          v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
-        }
-        dL_dalpha *= T;
-        last_alpha = alpha;
-        dL_dalpha += (-T_final / (1.0f - alpha)) * bg_dot;
-        const float dL_dG = a1.y * dL_dalpha;
-        const float gdx = Gv * dx, gdy = Gv * dy;
-        const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
-        const float dG_ddely = -gdy * a1.x - gdx * a0.w;
-        v[0] = dL_dG * dG_ddelx * ddelx_dx;
-        v[1] = dL_dG * dG_ddely * ddely_dy;
-        v[2] = -0.5f * gdx * dx * dL_dG;
-        v[3] = -0.5f * gdx * dy * dL_dG;
-        v[4] = -0.5f * gdy * dy * dL_dG;
-        v[5] = Gv * dL_dalpha;
+      for (int i = 0; i < kBatch / 32; i++) {
+        const int j = i * 32 + lane;
+        mask[i] = cull_round(r0, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
       }
-      const float r = warp_transpose_reduce10(v, lane);
-      if (my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9)) atomicAdd(&s.acc[j][my_comp], r);
+#pragma unroll
+      for (int i = kBatch / 32 - 1; i >= 0; i--) {
+        unsigned int m = mask[i];
+        while (m) {
+          const int bit = 31 - __clz(m);
+          m ^= 1u << bit;
+          const int j = i * 32 + bit;
+          const int pos = pos0 + j;
+          const float4 a0 = r0[j];
+          const float4 a1 = r1[j];
+          const float dx = a0.x - pxf, dy = a0.y - pyf;
+          const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+          const float Gv = __expf(power);
+          const float alpha = fminf(0.99f, a1.y * Gv);
+          const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+          if (!__any_sync(0xffffffffu, valid)) continue;
+          float v[10];
+#pragma unroll
+          for (int k = 0; k < 10; k++) v[k] = 0.0f;
+          if (valid) {
+            const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
+            const float col[4] = {a1.z, a1.w, a2.x, a2.y};
+            const float inv1ma = __fdividef(1.0f, 1.0f - alpha);
+            T = T * inv1ma;
+            const float dchannel_dcolor = alpha * T;
+            float dL_dalpha = 0.0f;
+#pragma unroll
+            for (int ch = 0; ch < CH; ch++) {
+              const float c = col[ch];
+              accum_rec[ch] = last_alpha * last_color[ch] + (1.0f - last_alpha) * accum_rec[ch];
+              last_color[ch] = c;
+              dL_dalpha += (c - accum_rec[ch]) * dL_dpix[ch];
+              v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
+            }
+            dL_dalpha *= T;
+            last_alpha = alpha;
+            dL_dalpha += bgT * inv1ma;
+            const float dL_dG = a1.y * dL_dalpha;
+            const float gdx = Gv * dx, gdy = Gv * dy;
+            const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
+            const float dG_ddely = -gdy * a1.x - gdx * a0.w;
+            v[0] = dL_dG * dG_ddelx * ddelx_dx;
+            v[1] = dL_dG * dG_ddely * ddely_dy;
+            v[2] = -0.5f * gdx * dx * dL_dG;
+            v[3] = -0.5f * gdx * dy * dL_dG;
+            v[4] = -0.5f * gdy * dy * dL_dG;
+            v[5] = Gv * dL_dalpha;
+          }
+          const float r = warp_transpose_reduce10(v, lane);
+          if (my_red) atomicAdd(&s.acc[j][my_comp], r);
+        }
+      }
     }
     __syncthreads();  // all warps finished batch b: accumulators complete, buffer b&1 free
     if (tid < cnt) {
-      const unsigned int id = __float_as_uint(s.r2[buf][tid].z);
+      const unsigned int id = __float_as_uint(r2[tid].z);
       float* dst = ws.grad_acc + ((size_t)n * G + id) * kAccFloats;
-      bool any = false;
-      float q[10];
-#pragma unroll
-      for (int k = 0; k < 10; k++) { q[k] = s.acc[tid][k]; any |= (q[k] != 0.0f); s.acc[tid][k] = 0.0f; }
+      float4* a4 = reinterpret_cast<float4*>(&s.acc[tid][0]);
+      const float4 q0 = a4[0], q1 = a4[1], q2 = a4[2];
+      const bool any = (q0.x != 0.0f) | (q0.y != 0.0f) | (q0.z != 0.0f) | (q0.w != 0.0f) | (q1.x != 0.0f) |
+                       (q1.y != 0.0f) | (q1.z != 0.0f) | (q1.w != 0.0f) | (q2.x != 0.0f) | (q2.y != 0.0f);
       if (any) {
-#pragma unroll
-        for (int k = 0; k < 10; k++)
-          if (k < 6 + CH) atomicAdd(dst + k, q[k]);
+        red_add_v4(dst, q0.x, q0.y, q0.z, q0.w);
+        red_add_v4(dst + 4, q1.x, q1.y, q1.z, q1.w);
+        red_add_v4(dst + 8, q2.x, q2.y, 0.0f, 0.0f);
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        a4[0] = z; a4[1] = z; a4[2] = z;
       }
     }
     __syncthreads();  // accumulators re-zeroed and record ids read before the buffer is reused

@@ -19,7 +19,10 @@ from ._lib import COV_FULL9, COV_TRIU6, DEPTH_MODES, SH_G3M, SH_GM3, TsplatLayou
 # capacity of the (tile, Gaussian) pair list, in pairs per (view, Gaussian); grows when a call
 # reports that it came close (see _Capacity)
 _DEFAULT_PAIRS_PER_GAUSSIAN = float(os.environ.get("TSPLAT_PAIRS_PER_GAUSSIAN", "8"))
-_CHECK_MODE = os.environ.get("TSPLAT_CHECK", "deferred")  # "deferred" | "sync"
+# "auto": the first call of a problem shape waits for the device's pair count (and retries with a larger
+# list if it overflowed); afterwards the capacity tracks 2x the last observed count and calls are
+# asynchronous.  "sync": every call waits.  "deferred": never wait (overflow surfaces at backward / next call).
+_CHECK_MODE = os.environ.get("TSPLAT_CHECK", "auto")
 
 
 class OverflowError_(RuntimeError):
@@ -33,6 +36,7 @@ class _Capacity:
     def __init__(self):
         self.cap = {}
         self.pending = {}
+        self.calibrated = set()  # keys whose pair count has been observed at least once
         self.unchecked = []  # (host, event, d_cap) of backward calls launched before their status arrived
 
     def check_unchecked(self):
@@ -68,12 +72,17 @@ class _Capacity:
         event.synchronize()
         del self.pending[key]
         st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
-        if key in self.cap and st.num_rendered * 1.25 > self.cap[key]:
-            self.cap[key] = min(int(st.num_rendered * 1.6) + 4096, (1 << 30) - 1)
+        self.observe(key, st.num_rendered)
         return st
 
-    def grow(self, key, num_rendered):
-        self.cap[key] = min(int(num_rendered * 1.6) + 4096, (1 << 30) - 1)
+    def observe(self, key, num_rendered):
+        """Keep the capacity at >= 2x the last observed pair count (never shrinks)."""
+        self.calibrated.add(key)
+        want = min(int(num_rendered * 2) + 4096, (1 << 30) - 1)
+        if want > self.cap.get(key, 0):
+            self.cap[key] = want
+
+    grow = observe
 
 
 _capacity = _Capacity()
@@ -91,7 +100,7 @@ class RenderConfig:
     sh_l4: int = 1
     want_radii: bool = False
     want_means2d_grad: bool = False
-    check: str | None = None   # None -> TSPLAT_CHECK env ("deferred" default)
+    check: str | None = None   # None -> TSPLAT_CHECK env ("auto" default)
     d_cap: int | None = None
 
 
@@ -170,9 +179,11 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
                                             C.c_void_p(stream.cuda_stream)), "tsplat_status_read")
             event = torch.cuda.Event()
             event.record(stream)
-            if check == "sync":
+            if check == "sync" or (check == "auto" and key not in _capacity.calibrated and not cfg.d_cap):
                 event.synchronize()
                 st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
+                if not cfg.d_cap:
+                    _capacity.observe(key, st.num_rendered)
                 if st.overflow:
                     if cfg.d_cap:
                         raise OverflowError_(f"pair list overflow: D={st.num_rendered} > d_cap={d_cap}")
