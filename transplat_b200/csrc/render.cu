@@ -2,47 +2,67 @@
 //
 // One CTA per (view, tile); grid = N*T, so every view of the call renders in one launch.  The
 // tile's slice of the depth-sorted record arrays (3 x float4 per entry, written by
-// ranges_gather_kernel) is contiguous, so batches of 256 entries are staged into shared memory
-// with 1-D TMA bulk copies completing on mbarriers, double-buffered: thread 0 issues batch b+1
-// while all 8 warps composite batch b from shared-memory broadcasts.  Colour (3 channels) and the
-// depth feature (4th channel) are composited in the same pass (the reference renders depth with a
-// second full pass, cuda_splatting.py:404).  Termination is voted per warp (__all_sync) and per
-// CTA (__syncthreads_count), as the reference does per CTA.
+// ranges_gather_kernel) is contiguous in HBM and is streamed through a shared-memory RING of
+// kStages stages x kStageEntries entries by a dedicated producer warp with 1-D TMA bulk copies
+// (cp.async.bulk -> mbarrier complete_tx).  The 8 consumer warps (one 8x4 pixel block each) run
+// DECOUPLED: each waits on a stage's `full` barrier, culls the stage's entries against its own
+// pixel block (conservative extents, exact in effect), composites the survivors, and arrives on the
+// stage's `empty` barrier; the producer refills a stage once all 8 warps have released it.  Depth
+// order makes consecutive entries spatially clustered, so per-batch CTA-wide barriers left warps
+// idle ~40% of the time; the ring lets them drift up to kStages-1 stages apart.
+// Colour (3 channels) and the depth feature (4th channel) are composited in the same pass (the
+// reference renders depth with a second full pass, cuda_splatting.py:404).
 #include <cuda_fp16.h>
 
 #include "common.cuh"
 
 namespace tsplat {
 
-struct RenderSmem {
-  float4 r0[2][kBatch];
-  float4 r1[2][kBatch];
-  float4 r2[2][kBatch];
-  uint64_t full[2];
+constexpr int kStageEntries = 64;  // list entries per ring stage (2 cull rounds of 32)
+constexpr int kStages = 8;         // ring depth: warps of a tile may drift 7 stages (448 entries) apart
+constexpr int kConsumerWarps = kTilePix / 32;     // 8
+constexpr int kRenderThreads = kTilePix + 32;     // + the producer warp
+
+struct RingSmem {
+  float4 r0[kStages][kStageEntries];  // x, y, conic.x, conic.y
+  float4 r1[kStages][kStageEntries];  // conic.z, opacity, r, g
+  float4 r2[kStages][kStageEntries];  // b, depth feature, bits(Gaussian id), packed fp16 extents
+  uint64_t full[kStages];
+  uint64_t empty[kStages];
+  int done_warps;
 };
 
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ int ld_volatile_smem(const int* p) {
+  int v;
+  asm volatile("ld.volatile.shared::cta.s32 %0, [%1];" : "=r"(v) : "r"(smem_u32(p)) : "memory");
+  return v;
+}
+
 template <class Smem>
-__device__ __forceinline__ void issue_batch(Smem& s, int buf, const Workspace& ws, unsigned int first,
+__device__ __forceinline__ void issue_stage(Smem& s, int stage, const Workspace& ws, unsigned int first,
                                             unsigned int cnt) {
   const uint32_t bytes = cnt * 16u;
-  mbar_expect_tx(&s.full[buf], 3u * bytes);
-  bulk_g2s(s.r0[buf], ws.rec0 + first, bytes, &s.full[buf]);
-  bulk_g2s(s.r1[buf], ws.rec1 + first, bytes, &s.full[buf]);
-  bulk_g2s(s.r2[buf], ws.rec2 + first, bytes, &s.full[buf]);
+  mbar_expect_tx(&s.full[stage], 3u * bytes);
+  bulk_g2s(s.r0[stage], ws.rec0 + first, bytes, &s.full[stage]);
+  bulk_g2s(s.r1[stage], ws.rec1 + first, bytes, &s.full[stage]);
+  bulk_g2s(s.r2[stage], ws.rec2 + first, bytes, &s.full[stage]);
 }
 
 // Pixel <-> thread mapping: warp w owns an 8x4 pixel block of the 16x16 tile (2 block columns x 4
 // block rows), lane l the pixel (l & 7, l >> 3) of it.  A compact block makes the per-warp culling
-// below effective (the mapping itself is invisible in the results).
+// effective (the mapping itself is invisible in the results).
 __device__ __forceinline__ void pixel_of_thread(int tid, int& bx, int& by, int& lx, int& ly) {
   const int warp = tid >> 5, lane = tid & 31;
   bx = (warp & 1) * 8; by = (warp >> 1) * 4;
   lx = lane & 7; ly = lane >> 3;
 }
 
-// Per-warp culling of one staged batch: bit l of mask[i] is set iff entry 32*i + l can touch the
-// warp's block [X0, X0+7] x [Y0, Y0+3] according to the conservative extents packed in rec2.w
-// (cull_extent, binning.cu).  One entry per lane, 8 rounds per 256-entry batch.
+// Per-warp culling: bit l of the result is set iff entry j (one per lane) can touch the warp's
+// block [X0, X0+7] x [Y0, Y0+3] according to the conservative extents packed in rec2.w
+// (cull_extent, binning.cu).
 __device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0, const float4* __restrict__ r2,
                                                    int j, bool in_range, float X0, float Y0) {
   bool hit = false;
@@ -56,14 +76,51 @@ __device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0
   return __ballot_sync(0xffffffffu, hit);
 }
 
+// ---------------------------------------------------------------------------------------------
+// Forward
+// ---------------------------------------------------------------------------------------------
 template <int CH>
-__global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, int H, int W,
-                                                                  const TsplatCamera* __restrict__ cams,
-                                                                  float* __restrict__ out_color,
-                                                                  float* __restrict__ out_depth) {
-  __shared__ __align__(128) RenderSmem s;
-  const int tid = threadIdx.x, lane = tid & 31;
+__global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspace ws, int H, int W,
+                                                                        const TsplatCamera* __restrict__ cams,
+                                                                        float* __restrict__ out_color,
+                                                                        float* __restrict__ out_depth) {
+  __shared__ __align__(128) RingSmem s;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
+  const uint2 range = ws.ranges[blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int nb = (total + kStageEntries - 1) / kStageEntries;
+
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < kStages; i++) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], kConsumerWarps); }
+    s.done_warps = 0;
+    mbar_fence_init();
+  }
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    // ---------------- producer: one lane streams the tile's list through the ring ----------------
+    if (lane != 0) return;
+    int issued = 0;
+    for (int b = 0; b < nb; b++) {
+      const int st = b % kStages, k = b / kStages;
+      bool stop = false;
+      if (b >= kStages) {  // wait until all 8 warps released the batch that occupied this stage
+        while (!mbar_try_wait(&s.empty[st], (unsigned)(k - 1) & 1u))
+          if (ld_volatile_smem(&s.done_warps) == kConsumerWarps) { stop = true; break; }
+      }
+      if (stop || ld_volatile_smem(&s.done_warps) == kConsumerWarps) break;  // every pixel saturated
+      issue_stage(s, st, ws, range.x + (unsigned)b * kStageEntries,
+                  (unsigned)min(kStageEntries, total - b * kStageEntries));
+      issued = b + 1;
+    }
+    // never leave the CTA with a bulk copy still in flight into its shared memory
+    for (int b = max(0, issued - kStages); b < issued; b++) mbar_wait(&s.full[b % kStages], (unsigned)(b / kStages) & 1u);
+    return;
+  }
+
+  // ---------------- consumers ----------------
   const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
   int bx, by, lx, ly;
   pixel_of_thread(tid, bx, by, lx, ly);
@@ -71,17 +128,6 @@ __global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, 
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
   const float X0 = (float)(tx * kTile + bx), Y0 = (float)(ty * kTile + by);
-  const uint2 range = ws.ranges[blockIdx.x];
-  const int total = (int)(range.y - range.x);
-  const int nb = (total + kBatch - 1) / kBatch;
-
-  if (tid == 0) {
-    mbar_init(&s.full[0], 1);
-    mbar_init(&s.full[1], 1);
-    mbar_fence_init();
-    if (nb > 0) issue_batch(s, 0, ws, range.x, (unsigned)min(kBatch, total));
-  }
-  __syncthreads();
 
   float T = 1.0f;
   float C[CH];
@@ -89,58 +135,64 @@ __global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, 
   for (int ch = 0; ch < CH; ch++) C[ch] = 0.0f;
   unsigned int last_contributor = 0;
   bool done = !inside;
-  int consumed = 0;  // batches whose barrier has been waited on
+  bool warp_done = __all_sync(0xffffffffu, done);
+  if (warp_done && lane == 0) atomicAdd(&s.done_warps, 1);
 
   for (int b = 0; b < nb; b++) {
-    // everyone is past batch b-1 => buffer (b+1)&1 is free; also the CTA-wide termination vote
-    const int num_done = __syncthreads_count(done);
-    if (num_done == kTilePix) break;
-    if (tid == 0 && b + 1 < nb)
-      issue_batch(s, (b + 1) & 1, ws, range.x + (unsigned)(b + 1) * kBatch,
-                  (unsigned)min(kBatch, total - (b + 1) * kBatch));
-    const int buf = b & 1;
-    mbar_wait(&s.full[buf], (b >> 1) & 1);
-    consumed = b + 1;
-    if (__all_sync(0xffffffffu, done)) continue;  // this warp has finished; keep voting with the CTA
-    const int cnt = min(kBatch, total - b * kBatch);
-    const float4* __restrict__ r0 = s.r0[buf];
-    const float4* __restrict__ r1 = s.r1[buf];
-    const float4* __restrict__ r2 = s.r2[buf];
-    unsigned int mask[kBatch / 32];
+    const int st = b % kStages;
+    const unsigned int par = (unsigned)(b / kStages) & 1u;
+    if (!warp_done) {
+      mbar_wait(&s.full[st], par);  // this warp still needs data, so the producer keeps going
+    } else {
+      bool quit = false;
+      while (!mbar_try_wait(&s.full[st], par))
+        if (ld_volatile_smem(&s.done_warps) == kConsumerWarps) { quit = true; break; }
+      if (quit) break;
+    }
+    if (!warp_done) {
+      const int cnt = min(kStageEntries, total - b * kStageEntries);
+      const float4* __restrict__ r0 = s.r0[st];
+      const float4* __restrict__ r1 = s.r1[st];
+      const float4* __restrict__ r2 = s.r2[st];
+      unsigned int mask[kStageEntries / 32];
 #pragma unroll
-    for (int i = 0; i < kBatch / 32; i++) mask[i] = cull_round(r0, r2, i * 32 + lane, i * 32 + lane < cnt, X0, Y0);
-    const unsigned int base = (unsigned int)(b * kBatch) + 1u;  // 1-based list position of entry 0
+      for (int i = 0; i < kStageEntries / 32; i++)
+        mask[i] = cull_round(r0, r2, i * 32 + lane, i * 32 + lane < cnt, X0, Y0);
+      const unsigned int base = (unsigned int)(b * kStageEntries) + 1u;  // 1-based list position of entry 0
 #pragma unroll
-    for (int i = 0; i < kBatch / 32; i++) {
-      unsigned int m = mask[i];
-      if (m == 0u) continue;
-      if (__all_sync(0xffffffffu, done)) break;  // warp-level early out, once per 32 entries
-      while (m) {
-        const int j = i * 32 + (__ffs(m) - 1);
-        m &= m - 1u;
-        const float4 a0 = r0[j];
-        const float4 a1 = r1[j];
-        const float dx = a0.x - pxf, dy = a0.y - pyf;
-        const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
-        if (done || power > 0.0f) continue;
-        const float alpha = fminf(0.99f, a1.y * __expf(power));
-        if (alpha < 1.0f / 255.0f) continue;
-        const float test_T = T * (1.0f - alpha);
-        if (test_T < 0.0001f) { done = true; continue; }
-        const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
-        const float w = alpha * T;
-        C[0] += a1.z * w;
-        C[1] += a1.w * w;
-        C[2] += a2.x * w;
-        if (CH == 4) C[3] += a2.y * w;
-        T = test_T;
-        last_contributor = base + (unsigned int)j;
+      for (int i = 0; i < kStageEntries / 32; i++) {
+        unsigned int m = mask[i];
+        while (m) {
+          const int j = i * 32 + (__ffs(m) - 1);
+          m &= m - 1u;
+          const float4 a0 = r0[j];
+          const float4 a1 = r1[j];
+          const float dx = a0.x - pxf, dy = a0.y - pyf;
+          const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+          if (done || power > 0.0f) continue;
+          const float alpha = fminf(0.99f, a1.y * __expf(power));
+          if (alpha < 1.0f / 255.0f) continue;
+          const float test_T = T * (1.0f - alpha);
+          if (test_T < 0.0001f) { done = true; continue; }
+          const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
+          const float w = alpha * T;
+          C[0] += a1.z * w;
+          C[1] += a1.w * w;
+          C[2] += a2.x * w;
+          if (CH == 4) C[3] += a2.y * w;
+          T = test_T;
+          last_contributor = base + (unsigned int)j;
+        }
+      }
+      if (__all_sync(0xffffffffu, done)) {
+        warp_done = true;
+        if (lane == 0) atomicAdd(&s.done_warps, 1);
       }
     }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s.empty[st]);
+    if (warp_done && ld_volatile_smem(&s.done_warps) == kConsumerWarps) break;
   }
-  // never leave the CTA with a bulk copy still in flight into its shared memory
-  // (if the loop broke at the vote of batch `consumed`, that batch's copy was already issued)
-  if (tid == 0 && consumed < nb) mbar_wait(&s.full[consumed & 1], (consumed >> 1) & 1);
   if (inside) {
     const size_t pix = (size_t)py * W + px;
     const size_t P = (size_t)H * W;
@@ -158,21 +210,25 @@ __global__ void __launch_bounds__(kTilePix) render_forward_kernel(Workspace ws, 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Backward: back-to-front over the same list.  Per entry the 10 gradient components
-// (mean2D.xy, conic.xyw, opacity, colour[CH]) are pre-reduced over the 32 pixels of each warp with
-// a 12-shuffle transpose-reduction, added into a per-batch shared-memory accumulator
-// (red.shared), and flushed with ONE global reduction per (tile, Gaussian, component) instead of
-// one atomic per (pixel, Gaussian, component) as the reference does.
+// Backward: back-to-front over the same list through the same kind of ring.  Per entry the 10
+// gradient components (mean2D.xy, conic.xyw, opacity, colour[CH]) are pre-reduced over the 32
+// pixels of each warp with a 12-shuffle transpose-reduction and added into the stage's
+// shared-memory accumulator (red.shared).  When all 8 warps have released a stage, the PRODUCER
+// warp flushes its accumulators with three 16-B vector reductions per (tile, Gaussian)
+// (red.global.add.v4.f32) and refills the stage: the flush is off the consumers' critical path, and
+// global reductions are one per (tile, Gaussian) instead of one atomic per (pixel, Gaussian,
+// component) as in the reference.
 // ---------------------------------------------------------------------------------------------
-struct RenderBwdSmem {
-  float4 r0[2][kBatch];
-  float4 r1[2][kBatch];
-  float4 r2[2][kBatch];
-  float acc[kBatch][kAccFloats];
-  uint64_t full[2];
+struct RingBwdSmem {
+  float4 r0[kStages][kStageEntries];
+  float4 r1[kStages][kStageEntries];
+  float4 r2[kStages][kStageEntries];
+  float acc[kStages][kStageEntries][kAccFloats];
+  uint64_t full[kStages];
+  uint64_t empty[kStages];
 };
 
-// Reduce v[0..9] over the warp.  On return lane L holds in `out` the full sum of component
+// Reduce v[0..9] over the warp.  On return lane L holds the full sum of component
 // comp_of_lane(L) (see below); lanes L and L^1 hold the same component.
 __device__ __forceinline__ float warp_transpose_reduce10(float (&v)[10], int lane) {
   const unsigned int full = 0xffffffffu;
@@ -225,7 +281,6 @@ __device__ __forceinline__ float warp_transpose_reduce10(float (&v)[10], int lan
 // component index held by `lane` after warp_transpose_reduce10, or -1 (padding slot)
 __device__ __forceinline__ int comp_of_lane(int lane) {
   const int h16 = (lane >> 4) & 1, h8 = (lane >> 3) & 1, h4 = (lane >> 2) & 1, h2 = (lane >> 1) & 1;
-  // round 3 index within b[0..3]: i3 = h2 + 2*h4 ; round 2 index within a[0..5]: i2 = i3' + 3*h8
   const int ib = h2 + 2 * h4;          // slot in b[] (0..3), 3 is padding
   if (ib == 3) return -1;
   const int ia = ib + 3 * h8;          // slot in a[] (0..5), 5 is padding
@@ -238,15 +293,76 @@ __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float 
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+// producer-side flush of one released stage: lane handles entries lane, lane+32
+__device__ __forceinline__ void flush_stage(RingBwdSmem& s, int st, int cnt, int lane, float* __restrict__ grad_acc,
+                                            size_t view_base) {
+#pragma unroll
+  for (int j = lane; j < kStageEntries; j += 32) {
+    if (j < cnt) {
+      const unsigned int id = __float_as_uint(s.r2[st][j].z);
+      float4* a4 = reinterpret_cast<float4*>(&s.acc[st][j][0]);
+      const float4 q0 = a4[0], q1 = a4[1], q2 = a4[2];
+      const bool any = (q0.x != 0.0f) | (q0.y != 0.0f) | (q0.z != 0.0f) | (q0.w != 0.0f) | (q1.x != 0.0f) |
+                       (q1.y != 0.0f) | (q1.z != 0.0f) | (q1.w != 0.0f) | (q2.x != 0.0f) | (q2.y != 0.0f);
+      if (any) {
+        float* dst = grad_acc + (view_base + id) * kAccFloats;
+        red_add_v4(dst, q0.x, q0.y, q0.z, q0.w);
+        red_add_v4(dst + 4, q1.x, q1.y, q1.z, q1.w);
+        red_add_v4(dst + 8, q2.x, q2.y, 0.0f, 0.0f);
+        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+        a4[0] = z; a4[1] = z; a4[2] = z;
+      }
+    }
+  }
+}
+
 template <int CH>
-__global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws, int H, int W, int G,
-                                                                   const TsplatCamera* __restrict__ cams,
-                                                                   const float* __restrict__ dL_dcolor,
-                                                                   const float* __restrict__ dL_ddepth) {
+__global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspace ws, int H, int W, int G,
+                                                                         const TsplatCamera* __restrict__ cams,
+                                                                         const float* __restrict__ dL_dcolor,
+                                                                         const float* __restrict__ dL_ddepth) {
   extern __shared__ __align__(128) unsigned char bsmem_raw[];
-  RenderBwdSmem& s = *reinterpret_cast<RenderBwdSmem*>(bsmem_raw);
-  const int tid = threadIdx.x, lane = tid & 31;
+  RingBwdSmem& s = *reinterpret_cast<RingBwdSmem*>(bsmem_raw);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
+  const uint2 range = ws.ranges[blockIdx.x];
+  const int total = (int)(range.y - range.x);
+  const int nb = (total + kStageEntries - 1) / kStageEntries;
+
+  // batch b (b = 0 is the END of the list) covers sorted entries [lo_b, hi_b)
+  auto batch_hi = [&](int b) { return (int)range.y - b * kStageEntries; };
+  auto batch_lo = [&](int b) { return max((int)range.x, (int)range.y - (b + 1) * kStageEntries); };
+
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < kStages; i++) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], kConsumerWarps); }
+    mbar_fence_init();
+  }
+  for (int i = tid; i < kStages * kStageEntries * kAccFloats; i += kRenderThreads) (&s.acc[0][0][0])[i] = 0.0f;
+  __syncthreads();
+
+  if (warp == kConsumerWarps) {
+    // ---------------- producer + flusher (whole warp) ----------------
+    const size_t view_base = (size_t)n * G;
+    for (int b = 0; b < nb; b++) {
+      const int st = b % kStages;
+      if (b >= kStages) {
+        const int pb = b - kStages;  // the batch that occupied this stage
+        mbar_wait(&s.empty[st], (unsigned)(pb / kStages) & 1u);
+        flush_stage(s, st, batch_hi(pb) - batch_lo(pb), lane, ws.grad_acc, view_base);
+        __syncwarp();  // every lane has read its record ids before the stage is overwritten
+      }
+      if (lane == 0) issue_stage(s, st, ws, (unsigned)batch_lo(b), (unsigned)(batch_hi(b) - batch_lo(b)));
+    }
+    for (int pb = max(0, nb - kStages); pb < nb; pb++) {
+      const int st = pb % kStages;
+      mbar_wait(&s.empty[st], (unsigned)(pb / kStages) & 1u);
+      flush_stage(s, st, batch_hi(pb) - batch_lo(pb), lane, ws.grad_acc, view_base);
+    }
+    return;
+  }
+
+  // ---------------- consumers ----------------
   const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
   int bx, by, lx, ly;
   pixel_of_thread(tid, bx, by, lx, ly);
@@ -254,24 +370,8 @@ __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws,
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
   const float X0 = (float)(tx * kTile + bx), Y0 = (float)(ty * kTile + by);
-  const uint2 range = ws.ranges[blockIdx.x];
-  const int total = (int)(range.y - range.x);
-  const int nb = (total + kBatch - 1) / kBatch;
   const size_t P = (size_t)H * W;
   const size_t pix = (size_t)py * W + px;
-
-  // batch b (b = 0 is the END of the list) covers sorted entries [lo_b, hi_b)
-  auto batch_hi = [&](int b) { return (int)range.y - b * kBatch; };
-  auto batch_lo = [&](int b) { return max((int)range.x, (int)range.y - (b + 1) * kBatch); };
-
-  if (tid == 0) {
-    mbar_init(&s.full[0], 1);
-    mbar_init(&s.full[1], 1);
-    mbar_fence_init();
-    if (nb > 0) issue_batch(s, 0, ws, (unsigned)batch_lo(0), (unsigned)(batch_hi(0) - batch_lo(0)));
-  }
-  for (int i = tid; i < kBatch * kAccFloats; i += kTilePix) (&s.acc[0][0])[i] = 0.0f;
-  __syncthreads();
 
   const float T_final = inside ? ws.final_T[n * P + pix] : 0.0f;
   float T = T_final;
@@ -296,24 +396,22 @@ __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws,
   const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
 
   for (int b = 0; b < nb; b++) {
-    const int buf = b & 1;
-    const int lo = batch_lo(b), hi = batch_hi(b), cnt = hi - lo;
-    if (tid == 0 && b + 1 < nb)  // buffer (b+1)&1 was released by the barrier that ended batch b-1
-      issue_batch(s, (b + 1) & 1, ws, (unsigned)batch_lo(b + 1), (unsigned)(batch_hi(b + 1) - batch_lo(b + 1)));
-    mbar_wait(&s.full[buf], (b >> 1) & 1);
-    const float4* __restrict__ r0 = s.r0[buf];
-    const float4* __restrict__ r1 = s.r1[buf];
-    const float4* __restrict__ r2 = s.r2[buf];
+    const int st = b % kStages;
+    const int lo = batch_lo(b), cnt = batch_hi(b) - lo;
+    mbar_wait(&s.full[st], (unsigned)(b / kStages) & 1u);
+    const float4* __restrict__ r0 = s.r0[st];
+    const float4* __restrict__ r1 = s.r1[st];
+    const float4* __restrict__ r2 = s.r2[st];
     const int pos0 = lo - (int)range.x;  // 0-based list position of entry 0 of this batch
     if (pos0 < warp_last) {
-      unsigned int mask[kBatch / 32];
+      unsigned int mask[kStageEntries / 32];
 #pragma unroll
-      for (int i = 0; i < kBatch / 32; i++) {
+      for (int i = 0; i < kStageEntries / 32; i++) {
         const int j = i * 32 + lane;
         mask[i] = cull_round(r0, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
       }
 #pragma unroll
-      for (int i = kBatch / 32 - 1; i >= 0; i--) {
+      for (int i = kStageEntries / 32 - 1; i >= 0; i--) {
         unsigned int m = mask[i];
         while (m) {
           const int bit = 31 - __clz(m);
@@ -361,27 +459,12 @@ __global__ void __launch_bounds__(kTilePix) render_backward_kernel(Workspace ws,
             v[5] = Gv * dL_dalpha;
           }
           const float r = warp_transpose_reduce10(v, lane);
-          if (my_red) atomicAdd(&s.acc[j][my_comp], r);
+          if (my_red) atomicAdd(&s.acc[st][j][my_comp], r);
         }
       }
     }
-    __syncthreads();  // all warps finished batch b: accumulators complete, buffer b&1 free
-    if (tid < cnt) {
-      const unsigned int id = __float_as_uint(r2[tid].z);
-      float* dst = ws.grad_acc + ((size_t)n * G + id) * kAccFloats;
-      float4* a4 = reinterpret_cast<float4*>(&s.acc[tid][0]);
-      const float4 q0 = a4[0], q1 = a4[1], q2 = a4[2];
-      const bool any = (q0.x != 0.0f) | (q0.y != 0.0f) | (q0.z != 0.0f) | (q0.w != 0.0f) | (q1.x != 0.0f) |
-                       (q1.y != 0.0f) | (q1.z != 0.0f) | (q1.w != 0.0f) | (q2.x != 0.0f) | (q2.y != 0.0f);
-      if (any) {
-        red_add_v4(dst, q0.x, q0.y, q0.z, q0.w);
-        red_add_v4(dst + 4, q1.x, q1.y, q1.z, q1.w);
-        red_add_v4(dst + 8, q2.x, q2.y, 0.0f, 0.0f);
-        const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
-        a4[0] = z; a4[1] = z; a4[2] = z;
-      }
-    }
-    __syncthreads();  // accumulators re-zeroed and record ids read before the buffer is reused
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&s.empty[st]);
   }
 }
 
@@ -390,9 +473,9 @@ cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, f
   const int grid = ws.N * ws.T;
   if (grid == 0) return cudaSuccess;
   if (p.depth_mode != TSPLAT_DEPTH_NONE)
-    render_forward_kernel<4><<<grid, kTilePix, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
+    render_forward_kernel<4><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
   else
-    render_forward_kernel<3><<<grid, kTilePix, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
+    render_forward_kernel<3><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
   return cudaGetLastError();
 }
 
@@ -400,16 +483,16 @@ cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, 
                                    const float* dL_ddepth, cudaStream_t st) {
   const int grid = ws.N * ws.T;
   if (grid == 0) return cudaSuccess;
-  const int smem = (int)sizeof(RenderBwdSmem);
+  const int smem = (int)sizeof(RingBwdSmem);
   cudaError_t e;
   if (p.depth_mode != TSPLAT_DEPTH_NONE) {
     e = cudaFuncSetAttribute(render_backward_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    render_backward_kernel<4><<<grid, kTilePix, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
+    render_backward_kernel<4><<<grid, kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
   } else {
     e = cudaFuncSetAttribute(render_backward_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    render_backward_kernel<3><<<grid, kTilePix, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
+    render_backward_kernel<3><<<grid, kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
   }
   return cudaGetLastError();
 }
