@@ -227,7 +227,7 @@ def run_ours(args):
                    "api": "DecoderSplattingCUDA.forward(depth_mode='depth') + torch.autograd.grad"},
         "clocks": clocks,
         "e2e": e2e,
-        "gpu_launches": args.steps * (6 + sort_passes(VIEWS, T)),
+        "gpu_launches": args.steps * (7 + sort_passes(VIEWS, T)),  # cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd, render bwd, preprocess bwd
         "roofline": {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": round(top_bytes), "kernel_ms": round(kern[top], 4),

@@ -53,6 +53,12 @@ extern "C" {
 #define TSPLAT_COV_TRIU6 0 /* [G, 6] xx,xy,xz,yy,yz,zz (cuda_splatting.py:124,132)  */
 #define TSPLAT_COV_FULL9 1 /* [G, 3, 3] Gaussians.covariances (types.py:10)          */
 
+/* problem flags */
+#define TSPLAT_FLAG_REZERO_GRAD_ACC 1 /* tsplat_backward: clear the screen-space accumulators first.  The
+                                         forward pass leaves them zero, so the FIRST backward after a forward
+                                         needs no clearing; set this for every further backward over the same
+                                         forward state (retain_graph) */
+
 /* fused depth channel (render_depth_cuda, cuda_splatting.py:375-417) */
 #define TSPLAT_DEPTH_NONE 0
 #define TSPLAT_DEPTH_DEPTH 1
@@ -96,7 +102,7 @@ typedef struct TsplatProblem {
   int32_t cov_layout; /* TSPLAT_COV_*                                                            */
   int32_t depth_mode; /* TSPLAT_DEPTH_*; != NONE adds the fused 4th (depth) channel              */
   int32_t sh_l4;      /* 1: evaluate the l=4 band when sh_degree>=4, 0: ignore it   */
-  int32_t reserved0;
+  int32_t flags;      /* TSPLAT_FLAG_* bits                                                      */
   const float* means;   /* [B, G, 3]                                                             */
   const float* cov;     /* [B, G, 6] or [B, G, 3, 3]                                             */
   const float* sh;      /* [B, G, M, 3] / [B, G, 3, M] / colors_precomp [B, G, 3]                */
@@ -120,7 +126,8 @@ typedef struct TsplatLayout {
   uint64_t ranges;        /* uint2  [N*T]    [first, last) per (view, tile)                       */
   uint64_t final_T;       /* float  [N, H, W]                                                     */
   uint64_t n_contrib;     /* uint32 [N, H, W]                                                     */
-  uint64_t grad_acc;      /* float  [N, G, 12] screen-space gradient accumulators (backward)      */
+  uint64_t grad_acc;      /* float  [N, G, 12] screen-space gradient accumulators (zeroed by the forward,
+                             filled by the backward)                                                */
   int32_t tiles_x, tiles_y; /* grid                                                               */
   int32_t sort_bits;      /* number of key bits the sort covers                                   */
   int32_t sort_passes;

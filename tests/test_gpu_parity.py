@@ -177,3 +177,21 @@ def test_pack_cameras_device_matches_host_restatement():
                                      bg[0].cuda(), scale_invariant=inv).cpu()
         assert torch.equal(shared[:, 37:40], bg[0][None].expand(7, 3))
         assert torch.equal(shared[:, :37], got[:, :37])
+
+
+def test_backward_twice_over_one_forward_state():
+    """The forward leaves the screen-space accumulators zero; a second backward over the same forward
+    state (retain_graph=True) re-clears them (TSPLAT_FLAG_REZERO_GRAD_ACC) and returns the same gradients."""
+    from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+    from transplat_b200.synthetic import make_scene
+    sc = make_scene(n_ctx=1, h=24, w=24, n_views=2, seed=11, render_hw=(40, 56))
+    leaves = [t[None].cuda().requires_grad_(True) for t in (sc.means, sc.covariances, sc.harmonics, sc.opacities)]
+    dec = DecoderSplattingCUDA().cuda()
+    out = dec.forward(Gaussians(*leaves), sc.extrinsics[None].cuda(), sc.intrinsics[None].cuda(), sc.near[None].cuda(),
+                      sc.far[None].cuda(), (40, 56), depth_mode="depth")
+    loss = (out.color ** 2).sum() + out.depth.sum()
+    g1 = torch.autograd.grad(loss, leaves, retain_graph=True)
+    g2 = torch.autograd.grad(loss, leaves)
+    for a, b in zip(g1, g2):
+        assert float((a - b).abs().max()) <= 1e-5 * float(a.abs().max()) + 1e-12
+    assert float(g1[0].abs().max()) > 0

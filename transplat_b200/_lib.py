@@ -13,6 +13,7 @@ CSRC = os.path.join(_HERE, "csrc")
 TSPLAT_OK, TSPLAT_EINVAL, TSPLAT_ENOSPC, TSPLAT_ECUDA = 0, 1, 2, 3
 SH_GM3, SH_G3M = 0, 1
 COV_TRIU6, COV_FULL9 = 0, 1
+FLAG_REZERO_GRAD_ACC = 1
 DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
@@ -23,7 +24,7 @@ EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "ts
 class TsplatProblem(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "B", "G", "V", "H", "W", "sh_degree", "sh_coeffs", "sh_layout", "cov_layout", "depth_mode",
-        "sh_l4", "reserved0")] + [(n, C.c_void_p) for n in ("means", "cov", "sh", "opacity", "cams")]
+        "sh_l4", "flags")] + [(n, C.c_void_p) for n in ("means", "cov", "sh", "opacity", "cams")]
 
 
 class TsplatLayout(C.Structure):

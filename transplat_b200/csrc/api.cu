@@ -71,6 +71,7 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   out->sort_state = take(4ull * kRadix * out->num_sort_tiles * L.sort_passes);
   L.ranges = take(8ull * N * T);
   out->zero_end = off;
+  out->tile_order = take(4ull * N * T);
   // ---- per (view, Gaussian) state ----
   L.depths = take(4 * NG);
   L.radii = take(4 * NG);
@@ -121,6 +122,8 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   w.rec0 = reinterpret_cast<float4*>(b + F.rec0);
   w.rec1 = reinterpret_cast<float4*>(b + F.rec1);
   w.rec2 = reinterpret_cast<float4*>(b + F.rec2);
+  w.tile_order = reinterpret_cast<unsigned int*>(b + F.tile_order);
+  w.use_order = (uint64_t)N * (uint64_t)(L.tiles_x * L.tiles_y) <= (uint64_t)kOrderMaxTiles ? 1 : 0;
   w.scan_state = reinterpret_cast<unsigned long long*>(b + F.scan_state);
   w.sort_state = reinterpret_cast<unsigned int*>(b + F.sort_state);
   w.d_cap = d_cap;
@@ -210,15 +213,21 @@ int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_b
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
   cudaError_t e;
   prof_begin_forward();
-  {
-    StageTimer t(kStZero, st);
-    e = cudaMemsetAsync(static_cast<char*>(workspace) + F.zero_begin, 0, F.zero_end - F.zero_begin, st);
-  }
-  if (e != cudaSuccess) return cuda_fail("memset(control)", e);
+  e = cudaSuccess;
   if (p->G == 0) {
     // nothing to draw: background only.  num_rendered stays 0; the render kernel sees empty ranges.
+    StageTimer t(kStZero, st);
+    e = cudaMemsetAsync(static_cast<char*>(workspace) + F.zero_begin, 0, F.zero_end - F.zero_begin, st);
+    if (e != cudaSuccess) return cuda_fail("memset(control)", e);
+    ws.use_order = 0;
   } else {
-    { StageTimer t(kStPre, st); e = launch_preprocess(*p, ws, out_radii, st); }
+    // the preprocess kernel also zeroes the control / look-back / ranges region (nothing in it is
+    // touched before bin_emit) and the screen-space gradient accumulators of the Gaussians it keeps
+    {
+      StageTimer t(kStPre, st);
+      e = launch_preprocess(*p, ws, out_radii, static_cast<char*>(workspace) + F.zero_begin,
+                            F.zero_end - F.zero_begin, st);
+    }
     if (e != cudaSuccess) return cuda_fail("preprocess", e);
     { StageTimer t(kStBin, st); e = launch_bin_emit(*p, ws, st); }
     if (e != cudaSuccess) return cuda_fail("bin_emit", e);
@@ -243,10 +252,14 @@ int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_
   if (p->depth_mode != TSPLAT_DEPTH_NONE && !dL_ddepth) { set_error("depth_mode set but dL_ddepth is NULL"); return TSPLAT_EINVAL; }
   if (p->G == 0) return TSPLAT_OK;
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
-  const uint64_t NG = (uint64_t)p->B * p->V * p->G;
   cudaError_t e;
-  { StageTimer t(kStZeroB, st); e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * NG, st); }
-  if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
+  // grad_acc is zero after the forward (its preprocess clears the kept Gaussians' accumulators); a repeated
+  // backward over the same forward state asks for a fresh clear
+  if (p->flags & TSPLAT_FLAG_REZERO_GRAD_ACC) {
+    StageTimer t(kStZeroB, st);
+    e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * (uint64_t)p->B * p->V * p->G, st);
+    if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
+  }
   { StageTimer t(kStRenderB, st); e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, st); }
   if (e != cudaSuccess) return cuda_fail("render_backward", e);
   {

@@ -361,6 +361,48 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
     ws.rec1[j] = make_float4(co.z, co.w, f.x, f.y);
     ws.rec2[j] = make_float4(f.z, f.w, __uint_as_float(id), __uint_as_float(cull_extent(co.x, co.y, co.z, co.w)));
   }
+  if (!ws.use_order) return;
+  // The last CTA to finish orders the (view, tile) ids by list length, longest first (counting sort
+  // on length/16): the render kernels take their tile from this table, so the hardware CTA
+  // scheduler hands out the long lists first and the short ones fill the tail of the launch.
+  __shared__ unsigned int s_bucket[1024];
+  __shared__ unsigned int s_warpsum[8];
+  __shared__ bool s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&ws.ctl->gather_done, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int NT = ws.N * ws.T, tid = threadIdx.x;
+  for (int i = tid; i < 1024; i += 256) s_bucket[i] = 0;
+  __syncthreads();
+  auto bucket_of = [&](int i) {
+    const uint2 r = __ldcg(&ws.ranges[i]);
+    const unsigned int len = r.y - r.x;
+    return 1023u - min(1023u, len >> 4);  // bucket 0 = longest lists
+  };
+  for (int i = tid; i < NT; i += 256) atomicAdd(&s_bucket[bucket_of(i)], 1u);
+  __syncthreads();
+  {  // exclusive scan of the 1024 bucket counts: 4 per thread
+    unsigned int c[4], sum = 0;
+#pragma unroll
+    for (int k = 0; k < 4; k++) { c[k] = s_bucket[tid * 4 + k]; sum += c[k]; }
+    unsigned int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if ((tid & 31) >= d) incl += t;
+    }
+    if ((tid & 31) == 31) s_warpsum[tid >> 5] = incl;
+    __syncthreads();
+    unsigned int pre = incl - sum;
+    for (int w = 0; w < (tid >> 5); w++) pre += s_warpsum[w];
+#pragma unroll
+    for (int k = 0; k < 4; k++) { s_bucket[tid * 4 + k] = pre; pre += c[k]; }
+  }
+  __syncthreads();
+  for (int i = tid; i < NT; i += 256) ws.tile_order[atomicAdd(&s_bucket[bucket_of(i)], 1u)] = (unsigned int)i;
 }
 
 cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st) {

@@ -25,6 +25,7 @@ constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 constexpr int kMaxPasses = 8;
 constexpr int kBatch = 256;                 // list entries staged per TMA batch in the render kernels
+constexpr int kOrderMaxTiles = 8192;         // order (view, tile) CTAs heaviest-first only up to this many
 constexpr int kAccFloats = 12;              // screen-space gradient accumulators per (view, Gaussian)
 
 // Device-side control block at the start of the workspace (superset of TsplatStatus).
@@ -34,7 +35,8 @@ struct Control {
   unsigned int reserved;
   unsigned int scan_tile_counter;   // dynamic tile ids for bin_emit
   unsigned int sort_tile_counter[kMaxPasses];
-  unsigned int pad[3];
+  unsigned int gather_done;         // CTAs of ranges_gather that have finished (last one orders the tiles)
+  unsigned int pad[2];
   unsigned int hist[kMaxPasses][kRadix];  // global digit histograms (onesweep: one upfront sweep)
 };
 
@@ -57,6 +59,8 @@ struct Workspace {
   float4* rec0;  // x, y, conic.x, conic.y                      (sorted order)
   float4* rec1;  // conic.z, opacity, r, g
   float4* rec2;  // b, depth feature, bits(Gaussian id), 0
+  unsigned int* tile_order;        // (view, tile) ids, heaviest list first (render launch order)
+  int use_order;                   // 0: identity order (very many tiles: waves balance themselves)
   unsigned long long* scan_state;  // decoupled look-back words for bin_emit
   unsigned int* sort_state;        // [passes][sort tiles][256]
   unsigned long long d_cap;
@@ -67,7 +71,7 @@ struct Workspace {
 
 struct LayoutFull {
   TsplatLayout pub;
-  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, scan_state, sort_state, zero_begin, zero_end;
+  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, scan_state, sort_state, tile_order, zero_begin, zero_end;
   int num_scan_tiles, num_sort_tiles;
 };
 
@@ -76,7 +80,8 @@ Workspace resolve(const LayoutFull& L, void* base, uint64_t d_cap, int N);
 void set_error(const char* fmt, ...);
 
 // stage launchers (each only enqueues on `st`)
-cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, cudaStream_t st);
+cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, void* zero_ptr,
+                              uint64_t zero_bytes, cudaStream_t st);
 cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_sort(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_ranges_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
@@ -110,14 +115,16 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                : "memory");
 }
+// suspend-time hint (ns): a waiting warp sleeps in hardware instead of spinning on the issue port
+constexpr uint32_t kMbarSuspendNs = 2000;
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred p;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, p;\n\t}"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(kMbarSuspendNs)
       : "memory");
   return ok != 0;
 }

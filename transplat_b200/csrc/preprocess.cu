@@ -19,6 +19,8 @@ struct PreArgs {
   int cov_floats;  // 6 or 9
   int sh_floats;   // 3*M, or 3 for colors_precomp
   int bulk_ok;     // all slabs 16-B aligned
+  uint4* zero_ptr;              // control / look-back / ranges region to clear (replaces a memset launch)
+  unsigned long long zero_vec;  // its size in 16-B words
 };
 
 __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a, Workspace ws, int* out_radii) {
@@ -41,6 +43,13 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a
   const float* g_op = p.opacity + gbase;
 
   const bool bulk = a.bulk_ok && cnt == kPreBlock;
+  {  // grid-stride clear of the region bin_emit / sort / ranges expect to be zero
+    const unsigned long long nthr = (unsigned long long)gridDim.x * gridDim.y * kPreBlock;
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (unsigned long long i = ((unsigned long long)blockIdx.y * gridDim.x + blockIdx.x) * kPreBlock + tid;
+         i < a.zero_vec; i += nthr)
+      a.zero_ptr[i] = z;
+  }
   if (bulk) {
     if (tid == 0) {
       mbar_init(bar, 1);
@@ -162,6 +171,11 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a
     ws.tiles_touched[o] = touched;
     ws.clamped[o] = cl;
     if (out_radii) out_radii[o] = radius;
+    if (radius > 0) {  // render_backward accumulates into these; preprocess_backward reads them iff radius > 0
+      float4* ga = reinterpret_cast<float4*>(ws.grad_acc + o * kAccFloats);
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      ga[0] = z; ga[1] = z; ga[2] = z;
+    }
   }
 }
 
@@ -173,9 +187,12 @@ __global__ void mark_visible_kernel(int G, const float* __restrict__ means, cons
   present[i] = transform4x3(m, view).z > 0.2f;
 }
 
-cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, cudaStream_t st) {
+cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, void* zero_ptr,
+                              uint64_t zero_bytes, cudaStream_t st) {
   PreArgs a;
   a.p = p;
+  a.zero_ptr = static_cast<uint4*>(zero_ptr);
+  a.zero_vec = zero_bytes / 16;  // the region is carved in 256-B units
   a.cov_floats = p.cov_layout == TSPLAT_COV_TRIU6 ? 6 : 9;
   a.sh_floats = p.sh_coeffs > 0 ? 3 * p.sh_coeffs : 3;
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };

@@ -86,8 +86,9 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
                                                                         float* __restrict__ out_depth) {
   __shared__ __align__(128) RingSmem s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
-  const uint2 range = ws.ranges[blockIdx.x];
+  const int bid = ws.use_order ? (int)ws.tile_order[blockIdx.x] : (int)blockIdx.x;  // longest lists first
+  const int n = bid / ws.T, tile = bid - n * ws.T;
+  const uint2 range = ws.ranges[bid];
   const int total = (int)(range.y - range.x);
   const int nb = (total + kStageEntries - 1) / kStageEntries;
 
@@ -324,8 +325,9 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   extern __shared__ __align__(128) unsigned char bsmem_raw[];
   RingBwdSmem& s = *reinterpret_cast<RingBwdSmem*>(bsmem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int n = blockIdx.x / ws.T, tile = blockIdx.x - n * ws.T;
-  const uint2 range = ws.ranges[blockIdx.x];
+  const int bid = ws.use_order ? (int)ws.tile_order[blockIdx.x] : (int)blockIdx.x;  // longest lists first
+  const int n = bid / ws.T, tile = bid - n * ws.T;
+  const uint2 range = ws.ranges[bid];
   const int total = (int)(range.y - range.x);
   const int nb = (total + kStageEntries - 1) / kStageEntries;
 

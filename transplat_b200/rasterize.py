@@ -118,6 +118,7 @@ def _problem(cfg: RenderConfig, means, cov, sh, opacity, cams) -> TsplatProblem:
     else:
         p.sh_coeffs = sh.shape[2] if cfg.sh_layout == SH_GM3 else sh.shape[3]
     p.sh_layout, p.cov_layout, p.depth_mode, p.sh_l4 = cfg.sh_layout, cfg.cov_layout, cfg.depth_mode, cfg.sh_l4
+    p.flags = 0
     p.means, p.cov, p.sh, p.opacity, p.cams = (means.data_ptr(), cov.data_ptr(), sh.data_ptr(),
                                                opacity.data_ptr(), cams.data_ptr())
     return p
@@ -125,7 +126,7 @@ def _problem(cfg: RenderConfig, means, cov, sh, opacity, cams) -> TsplatProblem:
 
 class _State:
     """What backward needs from forward: the opaque workspace and the problem description."""
-    __slots__ = ("problem", "workspace", "d_cap", "layout", "key", "tensors", "status_host", "event")
+    __slots__ = ("problem", "workspace", "d_cap", "layout", "key", "tensors", "status_host", "event", "bwd_calls")
 
 
 def _check_inputs(means, cov, sh, opacity, cams, cfg):
@@ -196,6 +197,7 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
     state.problem, state.workspace, state.d_cap, state.layout, state.key = prob, ws, d_cap, layout, key
     state.tensors = (means, cov, sh, opacity, cams)
     state.status_host, state.event = host, event
+    state.bwd_calls = 0
     return color, depth, radii, state
 
 
@@ -237,6 +239,9 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
         g_op = torch.empty_like(opacity)
         g_m2d = (torch.empty((N, means.shape[1], 3), dtype=torch.float32, device=dev)
                  if cfg.want_means2d_grad else None)
+        # the forward leaves the screen-space accumulators zero; every further backward re-clears them
+        state.problem.flags = _lib.FLAG_REZERO_GRAD_ACC if state.bwd_calls else 0
+        state.bwd_calls += 1
         _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
                                      state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
                                      _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
