@@ -1,0 +1,72 @@
+"""Host-buffer pipeline for the render path: steps whose inputs live in PINNED HOST memory and whose
+results return to pinned host memory, software-pipelined over three CUDA streams (H2D, compute,
+D2H) with a small ring of device slots, so the PCIe copies of step i+1 / i-1 overlap the kernels of
+step i.  PyTorch is plumbing (streams, events, the caching allocator); the work inside ``step_fn``
+is the C-ABI library.
+
+The reference has no such layer: its decoder is fed by the encoder on the device
+(src/model/model_wrapper.py:137-145).  This is what a caller uses when the Gaussians come from
+somewhere else (a file, another process, another node) - and what ``bench.py`` times as ``e2e``.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict
+
+import torch
+
+
+class HostPipeline:
+    def __init__(self, device: torch.device, slots: int = 3):
+        self.device = device
+        self.slots = slots
+        self.h2d = torch.cuda.Stream(device)
+        self.d2h = torch.cuda.Stream(device)
+        self.compute = torch.cuda.current_stream(device)
+        self._dev_in = [None] * slots      # per-slot device input buffers (allocated once per shape)
+        self._keep = [None] * slots        # per-slot outputs kept alive until their D2H has finished
+        self._done = [None] * slots        # per-slot event: D2H of the step that last used the slot
+        self._i = 0
+
+    def _buffers(self, k: int, host_in: Dict[str, torch.Tensor]):
+        cur = self._dev_in[k]
+        if cur is None or any(cur[n].shape != t.shape or cur[n].dtype != t.dtype for n, t in host_in.items()):
+            cur = {n: torch.empty(t.shape, dtype=t.dtype, device=self.device) for n, t in host_in.items()}
+            self._dev_in[k] = cur
+        return cur
+
+    def submit(self, step_fn: Callable[[Dict[str, torch.Tensor]], Dict[str, torch.Tensor]],
+               host_in: Dict[str, torch.Tensor], host_out: Dict[str, torch.Tensor]) -> torch.cuda.Event:
+        """Enqueue one step.  ``host_in`` / ``host_out`` are pinned tensors; ``step_fn`` maps the device
+        copies of ``host_in`` to a dict of device results with the keys of ``host_out``.  Returns the event
+        that marks ``host_out`` complete.  The caller must not reuse a ``host_out`` buffer before then."""
+        k = self._i % self.slots
+        self._i += 1
+        if self._done[k] is not None:
+            self._done[k].synchronize()  # back-pressure: the slot's previous step has fully drained
+        dev = self._buffers(k, host_in)
+        with torch.cuda.stream(self.h2d):
+            for n, t in host_in.items():
+                dev[n].copy_(t, non_blocking=True)
+            ev_in = torch.cuda.Event()
+            ev_in.record(self.h2d)
+        self.compute.wait_event(ev_in)
+        out = step_fn(dev)
+        ev_c = torch.cuda.Event()
+        ev_c.record(self.compute)
+        self.d2h.wait_event(ev_c)
+        with torch.cuda.stream(self.d2h):
+            for n, h in host_out.items():
+                h.copy_(out[n].detach(), non_blocking=True)
+            ev_out = torch.cuda.Event()
+            ev_out.record(self.d2h)
+        # the H2D stream must not overwrite this slot's inputs before the compute that reads them is done
+        self.h2d.wait_event(ev_c)
+        self._keep[k] = out
+        self._done[k] = ev_out
+        return ev_out
+
+    def drain(self) -> None:
+        for ev in self._done:
+            if ev is not None:
+                ev.synchronize()
+        self._keep = [None] * self.slots
