@@ -59,6 +59,10 @@ extern "C" {
                                          needs no clearing; set this for every further backward over the same
                                          forward state (retain_graph) */
 
+#define TSPLAT_FLAG_SORT_ONESWEEP 2   /* tsplat_forward: bin with the global onesweep LSD radix sort over the full
+                                         (view*T + tile | depth) key instead of the default bucket path (count per
+                                         tile -> scan -> emit -> per-tile sort in shared memory).  Same results. */
+
 /* fused depth channel (render_depth_cuda, cuda_splatting.py:375-417) */
 #define TSPLAT_DEPTH_NONE 0
 #define TSPLAT_DEPTH_DEPTH 1

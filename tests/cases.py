@@ -26,6 +26,9 @@ def case(name: str):
     if name == "deg2_l1":          # SH degree 2 with 9 coefficients, level 1
         sc = make_scene(n_ctx=1, h=32, w=32, n_views=1, render_hw=(64, 64), seed=8, sh_degree=2)
         return _pack(sc, level=1, B=1, depth_mode=0, cov_mul=4.0, bg=(0.1, 0.1, 0.1))
+    if name == "dense_big":        # few tiles, very long lists: > 4096 and > 16384 pairs per tile (big-tile sort paths)
+        sc = make_scene(n_ctx=1, h=144, w=144, n_views=2, render_hw=(32, 48), seed=31)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=120.0, bg=(0.0, 0.0, 0.0))
     if name == "c2":               # BASELINE config 2: 131072 Gaussians, 4 views, 256x256, colour+depth
         sc = make_scene()
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))

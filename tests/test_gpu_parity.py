@@ -35,15 +35,32 @@ def _assert_reports(fwd, bwd):
                 assert v <= GRAD_RTOL, (k, bwd)
 
 
+@pytest.mark.parametrize("sort", ["bucket", "onesweep"])
 @pytest.mark.parametrize("name", ["tiny_l1", "deg2_l1", "small_l2_depth", "ragged_l2", "mid_l2"])
-def test_stage_by_stage_parity(name):
-    fwd, bwd = run_both(*case(name))
+def test_stage_by_stage_parity(name, sort):
+    """Both binning paths (per-tile bucket sort; global onesweep LSD radix sort) against the oracle."""
+    *args, cfg = case(name)
+    cfg.sort = sort
+    fwd, bwd = run_both(*args, cfg)
     _assert_reports(fwd, bwd)
 
 
-def test_c2_full_size_parity():
+def test_long_tile_lists_take_the_big_tile_sort_paths():
+    """6 tiles per view with 15 000 - 20 000 pairs each: the 128-KB shared-memory sort (<= 16384) and the in-place
+    global-memory sort (> 16384)."""
+    *args, cfg = case("dense_big")
+    cfg.sort = "bucket"
+    fwd, bwd = run_both(*args, cfg)
+    assert fwd["num_rendered_gpu"] > 6 * 4096
+    _assert_reports(fwd, bwd)
+
+
+@pytest.mark.parametrize("sort", ["bucket", "onesweep"])
+def test_c2_full_size_parity(sort):
     """BASELINE config 2 at full size (131072 Gaussians, 4 views, 256x256, colour+depth)."""
-    fwd, bwd = run_both(*case("c2"))
+    *args, cfg = case("c2")
+    cfg.sort = sort
+    fwd, bwd = run_both(*args, cfg)
     assert fwd["num_rendered_gpu"] > 1_000_000
     _assert_reports(fwd, bwd)
 

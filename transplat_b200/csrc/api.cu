@@ -67,11 +67,15 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   // ---- region zeroed at the start of every forward ----
   out->zero_begin = off;
   L.status = take(sizeof(Control));
+  L.ranges = take(8ull * N * T);
+  out->tile_count = take(4ull * N * T);
+  out->tile_cursor = take(4ull * N * T);
+  out->zero_mid = off;
   out->scan_state = take(8ull * out->num_scan_tiles);
   out->sort_state = take(4ull * kRadix * out->num_sort_tiles * L.sort_passes);
-  L.ranges = take(8ull * N * T);
   out->zero_end = off;
   out->tile_order = take(4ull * N * T);
+  out->big_list = take(4ull * N * T);
   // ---- per (view, Gaussian) state ----
   L.depths = take(4 * NG);
   L.radii = take(4 * NG);
@@ -123,6 +127,10 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   w.rec1 = reinterpret_cast<float4*>(b + F.rec1);
   w.rec2 = reinterpret_cast<float4*>(b + F.rec2);
   w.tile_order = reinterpret_cast<unsigned int*>(b + F.tile_order);
+  w.tile_count = reinterpret_cast<unsigned int*>(b + F.tile_count);
+  w.tile_cursor = reinterpret_cast<unsigned int*>(b + F.tile_cursor);
+  w.big_list = reinterpret_cast<unsigned int*>(b + F.big_list);
+  w.bucket = 1;
   w.use_order = (uint64_t)N * (uint64_t)(L.tiles_x * L.tiles_y) <= (uint64_t)kOrderMaxTiles ? 1 : 0;
   w.scan_state = reinterpret_cast<unsigned long long*>(b + F.scan_state);
   w.sort_state = reinterpret_cast<unsigned int*>(b + F.sort_state);
@@ -221,20 +229,28 @@ int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_b
     if (e != cudaSuccess) return cuda_fail("memset(control)", e);
     ws.use_order = 0;
   } else {
-    // the preprocess kernel also zeroes the control / look-back / ranges region (nothing in it is
-    // touched before bin_emit) and the screen-space gradient accumulators of the Gaussians it keeps
+    // the preprocess kernel also zeroes the control / counters / ranges region (nothing in it is
+    // touched before the binning kernels) and the screen-space gradient accumulators of the Gaussians it keeps
+    ws.bucket = (p->flags & TSPLAT_FLAG_SORT_ONESWEEP) ? 0 : 1;
     {
       StageTimer t(kStPre, st);
       e = launch_preprocess(*p, ws, out_radii, static_cast<char*>(workspace) + F.zero_begin,
-                            F.zero_end - F.zero_begin, st);
+                            (ws.bucket ? F.zero_mid : F.zero_end) - F.zero_begin, st);
     }
     if (e != cudaSuccess) return cuda_fail("preprocess", e);
-    { StageTimer t(kStBin, st); e = launch_bin_emit(*p, ws, st); }
-    if (e != cudaSuccess) return cuda_fail("bin_emit", e);
-    { StageTimer t(kStSort, st); e = launch_sort(*p, ws, st); }
-    if (e != cudaSuccess) return cuda_fail("sort", e);
-    { StageTimer t(kStRanges, st); e = launch_ranges_gather(*p, ws, st); }
-    if (e != cudaSuccess) return cuda_fail("ranges_gather", e);
+    if (ws.bucket) {
+      { StageTimer t(kStBin, st); e = launch_bucket_scan_emit(*p, ws, st); }
+      if (e != cudaSuccess) return cuda_fail("bucket_scan_emit", e);
+      { StageTimer t(kStSort, st); e = launch_bucket_sort_gather(*p, ws, st); }
+      if (e != cudaSuccess) return cuda_fail("bucket_sort_gather", e);
+    } else {
+      { StageTimer t(kStBin, st); e = launch_bin_emit(*p, ws, st); }
+      if (e != cudaSuccess) return cuda_fail("bin_emit", e);
+      { StageTimer t(kStSort, st); e = launch_sort(*p, ws, st); }
+      if (e != cudaSuccess) return cuda_fail("sort", e);
+      { StageTimer t(kStRanges, st); e = launch_ranges_gather(*p, ws, st); }
+      if (e != cudaSuccess) return cuda_fail("ranges_gather", e);
+    }
   }
   { StageTimer t(kStRender, st); e = launch_render_forward(*p, ws, out_color, out_depth, st); }
   if (e != cudaSuccess) return cuda_fail("render_forward", e);

@@ -25,6 +25,8 @@ constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 constexpr int kMaxPasses = 8;
 constexpr int kBatch = 256;                 // list entries staged per TMA batch in the render kernels
+constexpr int kSmallTileCap = 4096;          // bucket path: pairs per tile sorted by the small-tile kernel (32 KB smem)
+constexpr int kBigTileCap = 16384;           // ... by the big-tile kernel in shared memory (128 KB); beyond: in global memory
 constexpr int kOrderMaxTiles = 8192;         // order (view, tile) CTAs heaviest-first only up to this many
 constexpr int kAccFloats = 12;              // screen-space gradient accumulators per (view, Gaussian)
 
@@ -36,7 +38,8 @@ struct Control {
   unsigned int scan_tile_counter;   // dynamic tile ids for bin_emit
   unsigned int sort_tile_counter[kMaxPasses];
   unsigned int gather_done;         // CTAs of ranges_gather that have finished (last one orders the tiles)
-  unsigned int pad[2];
+  unsigned int num_big;             // bucket path: tiles whose list does not fit the small-tile sort kernel
+  unsigned int pad[1];
   unsigned int hist[kMaxPasses][kRadix];  // global digit histograms (onesweep: one upfront sweep)
 };
 
@@ -59,6 +62,10 @@ struct Workspace {
   float4* rec0;  // x, y, conic.x, conic.y                      (sorted order)
   float4* rec1;  // conic.z, opacity, r, g
   float4* rec2;  // b, depth feature, bits(Gaussian id), 0
+  unsigned int* tile_count;        // bucket path: pairs per (view, tile), counted by the preprocess kernel
+  unsigned int* tile_cursor;       // bucket path: emission cursors per (view, tile)
+  unsigned int* big_list;          // bucket path: (view, tile) ids with more than kSmallTileCap pairs
+  int bucket;                      // 1: bucket path (count -> scan -> emit -> per-tile sort), 0: onesweep LSD path
   unsigned int* tile_order;        // (view, tile) ids, heaviest list first (render launch order)
   int use_order;                   // 0: identity order (very many tiles: waves balance themselves)
   unsigned long long* scan_state;  // decoupled look-back words for bin_emit
@@ -71,7 +78,8 @@ struct Workspace {
 
 struct LayoutFull {
   TsplatLayout pub;
-  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, scan_state, sort_state, tile_order, zero_begin, zero_end;
+  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, scan_state, sort_state, tile_order, tile_count, tile_cursor, big_list,
+      zero_begin, zero_mid, zero_end;  // [zero_begin, zero_mid) is all the bucket path needs cleared
   int num_scan_tiles, num_sort_tiles;
 };
 
@@ -82,6 +90,8 @@ void set_error(const char* fmt, ...);
 // stage launchers (each only enqueues on `st`)
 cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* out_radii, void* zero_ptr,
                               uint64_t zero_bytes, cudaStream_t st);
+cudaError_t launch_bucket_scan_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_bucket_sort_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_sort(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_ranges_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);

@@ -23,6 +23,9 @@ _DEFAULT_PAIRS_PER_GAUSSIAN = float(os.environ.get("TSPLAT_PAIRS_PER_GAUSSIAN", 
 # list if it overflowed); afterwards the capacity tracks 2x the last observed count and calls are
 # asynchronous.  "sync": every call waits.  "deferred": never wait (overflow surfaces at backward / next call).
 _CHECK_MODE = os.environ.get("TSPLAT_CHECK", "auto")
+# binning path: "bucket" (count per tile -> scan -> emit -> per-tile shared-memory sort; default) or
+# "onesweep" (global LSD radix sort over the full 64-bit key); identical results
+_SORT_MODE = os.environ.get("TSPLAT_SORT", "bucket")
 
 
 class OverflowError_(RuntimeError):
@@ -102,6 +105,7 @@ class RenderConfig:
     want_means2d_grad: bool = False
     check: str | None = None   # None -> TSPLAT_CHECK env ("auto" default)
     d_cap: int | None = None
+    sort: str | None = None    # None -> TSPLAT_SORT env ("bucket" default) | "bucket" | "onesweep"
 
 
 def _ptr(t):
@@ -118,7 +122,7 @@ def _problem(cfg: RenderConfig, means, cov, sh, opacity, cams) -> TsplatProblem:
     else:
         p.sh_coeffs = sh.shape[2] if cfg.sh_layout == SH_GM3 else sh.shape[3]
     p.sh_layout, p.cov_layout, p.depth_mode, p.sh_l4 = cfg.sh_layout, cfg.cov_layout, cfg.depth_mode, cfg.sh_l4
-    p.flags = 0
+    p.flags = _lib.FLAG_SORT_ONESWEEP if (cfg.sort or _SORT_MODE) == "onesweep" else 0
     p.means, p.cov, p.sh, p.opacity, p.cams = (means.data_ptr(), cov.data_ptr(), sh.data_ptr(),
                                                opacity.data_ptr(), cams.data_ptr())
     return p
@@ -240,7 +244,8 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
         g_m2d = (torch.empty((N, means.shape[1], 3), dtype=torch.float32, device=dev)
                  if cfg.want_means2d_grad else None)
         # the forward leaves the screen-space accumulators zero; every further backward re-clears them
-        state.problem.flags = _lib.FLAG_REZERO_GRAD_ACC if state.bwd_calls else 0
+        if state.bwd_calls:
+            state.problem.flags |= _lib.FLAG_REZERO_GRAD_ACC
         state.bwd_calls += 1
         _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
                                      state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
