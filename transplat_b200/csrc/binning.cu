@@ -217,7 +217,14 @@ __global__ void __launch_bounds__(kSortThreads) onesweep_pass_kernel(Workspace w
     const unsigned int li = wbase + i * 32 + lane;
     const bool valid = li < n;
     const unsigned int dg = (unsigned int)(key[i] >> shift) & 255u;
-    const unsigned int same = __match_any_sync(0xffffffffu, valid ? dg : (256u + lane));
+    // peers with the same digit from 8 ballots (MATCH.ANY is microcoded and slow on sm_100)
+    unsigned int same = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int bit = 0; bit < 8; bit++) {
+      const unsigned int v = __ballot_sync(0xffffffffu, (dg >> bit) & 1u);
+      same &= ((dg >> bit) & 1u) ? v : ~v;
+    }
+    if (!valid) same = 1u << lane;
     const int leader = __ffs(same) - 1;
     unsigned int old = 0;
     if (valid && lane == leader) {

@@ -10,10 +10,11 @@
 //   3. bucket_emit_kernel: every (Gaussian, tile) pair takes a slot of its tile's segment from an
 //      atomic cursor and stores (depth bits << 32 | Gaussian id)
 //   4. tile_sort_gather_kernel: one CTA per tile sorts its segment by that 64-bit word in SHARED
-//      MEMORY (bitonic network; the word is unique, so the result equals the stable sort by depth
-//      of the Gaussian-ordered list) and writes keys, values and the gathered 48-B records in
-//      sorted order; tiles above kSmallTileCap go to a second launch with a 128-KB buffer, tiles
-//      above kBigTileCap are sorted in place in global memory by one CTA.
+//      MEMORY (the word is unique, so the result equals the stable sort by depth of the
+//      Gaussian-ordered list: 4-pass LSD radix sort on the depth half + a fix-up of equal-depth runs)
+//      and writes keys, values and the gathered 48-B records in sorted order; tiles above
+//      kSmallTileCap go to a second launch (bitonic network in a 128-KB buffer), tiles above
+//      kBigTileCap are sorted in place in global memory by one CTA.
 //
 // Why: at C2 (1.6 M pairs, 42 key bits) six LSD passes were latency-bound at ~26 us each plus a
 // 38-us scan/emit and a 38-us range/gather pass (272 us before render); each pair now crosses HBM
@@ -161,31 +162,68 @@ __global__ void __launch_bounds__(256) bucket_emit_kernel(Workspace ws, int G, u
 //    mirrors the partner), so a list of any length n sorts without padding: a comparator whose upper
 //    index is >= n would compare against +inf and is skipped.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void compare_exchange(unsigned long long* s, int i, int l) {
-  const unsigned long long a = s[i], b = s[l];
-  if (a > b) { s[i] = b; s[l] = a; }
+// One pass over the array executing R consecutive comparator steps (xor masks m[0..R-1], whose top
+// bits sit at consecutive positions p+R-1 .. p) on groups of 2^R elements held in registers: the
+// array crosses shared memory once per pass instead of once per step (the plain network is
+// shared-memory-bandwidth bound: 66 steps for 2048 words).  Elements at index >= n are +inf
+// (never stored); every comparator leaves the minimum at the lower index.
+template <int R>
+__device__ __forceinline__ void bitonic_pass(unsigned long long* s, int n, int np, int p, const int (&m)[3], int tid,
+                                             int nthreads) {
+  constexpr int E = 1 << R;
+  for (int t = tid; t < (np >> R); t += nthreads) {
+    const int base = ((t >> p) << (p + R)) | (t & ((1 << p) - 1));
+    int idx[E];
+    unsigned long long v[E];
+#pragma unroll
+    for (int a = 0; a < E; a++) {
+      int x = base;
+#pragma unroll
+      for (int r = 0; r < R; r++)
+        if (a & (1 << (R - 1 - r))) x ^= m[r];
+      idx[a] = x;
+      v[a] = x < n ? s[x] : ~0ull;
+    }
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+      const int ab = 1 << (R - 1 - r);
+#pragma unroll
+      for (int a = 0; a < E; a++) {
+        if (a & ab) continue;
+        const unsigned long long x = v[a], y = v[a | ab];
+        const bool a_low = idx[a] < idx[a | ab];  // the minimum goes to the lower index
+        if (a_low ? (x > y) : (x < y)) { v[a] = y; v[a | ab] = x; }
+      }
+    }
+#pragma unroll
+    for (int a = 0; a < E; a++)
+      if (idx[a] < n) s[idx[a]] = v[a];
+  }
+  __syncthreads();
 }
 
 // s: the n words (shared or global memory, private to this CTA).  All threads of the CTA call.
+// Bitonic network in ascending-only form: level k = [mirror step: i <-> i ^ (k-1)], then strides
+// k/4, k/8, ..., 1; steps are taken three at a time.
 __device__ __forceinline__ void bitonic_sort_words(unsigned long long* s, int n, int tid, int nthreads) {
   if (n < 2) return;
-  int np = 2;
-  while (np < n) np <<= 1;
-  const int half = np >> 1;
-  for (int k = 2; k <= np; k <<= 1) {
-    const int hk = k >> 1;
-    for (int t = tid; t < half; t += nthreads) {  // mirrored step
-      const int blk = t / hk, off = t - blk * hk;
-      const int i = blk * k + off, l = blk * k + (k - 1 - off);
-      if (l < n) compare_exchange(s, i, l);
-    }
-    __syncthreads();
-    for (int j = hk >> 1; j > 0; j >>= 1) {
-      for (int t = tid; t < half; t += nthreads) {
-        const int i = 2 * t - (t & (j - 1)), l = i + j;
-        if (l < n) compare_exchange(s, i, l);
+  int lg = 1;
+  while ((1 << lg) < n) lg++;
+  const int np = 1 << lg;
+  for (int mlev = 1; mlev <= lg; mlev++) {  // level k = 2^mlev has mlev steps: masks k-1, k/4, k/8, ..., 1
+    int step = 0;
+    while (step < mlev) {
+      const int R = min(3, mlev - step);
+      int m[3] = {0, 0, 0};
+      for (int r = 0; r < R; r++) {
+        const int st = step + r;
+        m[r] = st == 0 ? (1 << mlev) - 1 : 1 << (mlev - 1 - st);
       }
-      __syncthreads();
+      const int p = mlev - step - R;  // lowest top-bit position of the chunk
+      if (R == 3) bitonic_pass<3>(s, n, np, p, m, tid, nthreads);
+      else if (R == 2) bitonic_pass<2>(s, n, np, p, m, tid, nthreads);
+      else bitonic_pass<1>(s, n, np, p, m, tid, nthreads);
+      step += R;
     }
   }
 }
@@ -195,39 +233,174 @@ __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const uns
                                                   int bid, int G, unsigned long long* __restrict__ keys_out,
                                                   unsigned int* __restrict__ vals_out, int tid, int nthreads) {
   const size_t vbase = (size_t)(bid / ws.T) * G;
-  for (int j = tid; j < n; j += nthreads) {
-    const unsigned long long w = s[j];
-    const unsigned int id = (unsigned int)w;
-    keys_out[start + j] = ((unsigned long long)(unsigned int)bid << 32) | (w >> 32);
-    vals_out[start + j] = id;
-    const size_t o = vbase + id;
-    const float2 c = ws.xy[o];
-    const float4 co = ws.conic_opacity[o];
-    const float4 f = ws.rgbd[o];
-    ws.rec0[start + j] = make_float4(c.x, c.y, co.x, co.y);
-    ws.rec1[start + j] = make_float4(co.z, co.w, f.x, f.y);
-    ws.rec2[start + j] = make_float4(f.z, f.w, __uint_as_float(id), __uint_as_float(cull_extent(co.x, co.y, co.z, co.w)));
+  const unsigned long long hiw = (unsigned long long)(unsigned int)bid << 32;
+  constexpr int U = 4;  // entries in flight per thread: the gathers are L2-latency bound
+  for (int j0 = tid; j0 < n; j0 += U * nthreads) {
+    unsigned long long w[U];
+    float2 c[U];
+    float4 co[U], f[U];
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int j = j0 + u * nthreads;
+      w[u] = j < n ? s[j] : 0ull;
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int j = j0 + u * nthreads;
+      if (j < n) {
+        const size_t o = vbase + (unsigned int)w[u];
+        c[u] = ws.xy[o]; co[u] = ws.conic_opacity[o]; f[u] = ws.rgbd[o];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const int j = j0 + u * nthreads;
+      if (j < n) {
+        const unsigned int id = (unsigned int)w[u];
+        keys_out[start + j] = hiw | (w[u] >> 32);
+        vals_out[start + j] = id;
+        ws.rec0[start + j] = make_float4(c[u].x, c[u].y, co[u].x, co[u].y);
+        ws.rec1[start + j] = make_float4(co[u].z, co[u].w, f[u].x, f[u].y);
+        ws.rec2[start + j] = make_float4(f[u].z, f[u].w, __uint_as_float(id),
+                                         __uint_as_float(cull_extent(co[u].x, co[u].y, co[u].z, co[u].w)));
+      }
+    }
   }
 }
 
-__global__ void __launch_bounds__(256) tile_sort_gather_kernel(Workspace ws, int G,
-                                                               const unsigned long long* __restrict__ pairs,
-                                                               unsigned long long* __restrict__ keys_out,
-                                                               unsigned int* __restrict__ vals_out) {
-  __shared__ unsigned long long s[kSmallTileCap];
+// Small tiles (n <= kSmallTileCap): CTA-wide LSD radix sort of the words by their DEPTH half (4 passes
+// of 8 bits, in place in shared memory: a pass holds its words in registers between the load and the
+// scatter), then runs of equal depth - rare, short - are put in Gaussian order.  ~6x fewer
+// instructions than the bitonic network at n ~ 1600 (measured 70 M warp instructions per launch).
+constexpr int kTileSortThreads = 512;
+constexpr int kTileSortWarps = kTileSortThreads / 32;
+
+struct TileSortSmem {
+  unsigned long long words[kSmallTileCap];
+  unsigned int whist[kTileSortWarps][kRadix];  // per-warp digit counts -> exclusive prefixes over warps
+  unsigned int dexcl[kRadix];                  // exclusive offset of each digit in the CTA
+  unsigned int wscan[8];
+  unsigned int nruns;
+};
+
+template <int KPT>
+__device__ __forceinline__ void radix_sort_tile_by_depth(TileSortSmem& s, int n, int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  const int wbase = warp * (32 * KPT);
+#pragma unroll 1
+  for (int pass = 0; pass < 4; pass++) {
+    const int shift = 32 + 8 * pass;
+    for (int i = tid; i < kTileSortWarps * kRadix; i += kTileSortThreads) (&s.whist[0][0])[i] = 0u;
+    unsigned long long w[KPT];
+#pragma unroll
+    for (int i = 0; i < KPT; i++) {
+      const int li = wbase + i * 32 + lane;
+      w[i] = li < n ? s.words[li] : ~0ull;
+    }
+    __syncthreads();
+    unsigned short rank[KPT];
+#pragma unroll
+    for (int i = 0; i < KPT; i++) {  // warp-private ranking: step i ascending, lane ascending == current order
+      const bool valid = wbase + i * 32 + lane < n;
+      const unsigned int dg = (unsigned int)(w[i] >> shift) & 255u;
+      // peers with the same digit, from 8 ballots (MATCH.ANY is microcoded and slow on sm_100: it was 30 % of
+      // this kernel's stall samples)
+      unsigned int same = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+      for (int bit = 0; bit < 8; bit++) {
+        const unsigned int v = __ballot_sync(0xffffffffu, (dg >> bit) & 1u);
+        same &= ((dg >> bit) & 1u) ? v : ~v;
+      }
+      if (!valid) same = 1u << lane;
+      const int leader = __ffs(same) - 1;
+      unsigned int old = 0;
+      if (valid && lane == leader) {
+        old = s.whist[warp][dg];
+        s.whist[warp][dg] = old + __popc(same);
+      }
+      old = __shfl_sync(0xffffffffu, old, leader);
+      rank[i] = (unsigned short)(old + __popc(same & ((1u << lane) - 1u)));
+      __syncwarp();
+    }
+    __syncthreads();
+    unsigned int dcount = 0, incl = 0;
+    if (tid < kRadix) {  // thread d owns digit d
+#pragma unroll
+      for (int wv = 0; wv < kTileSortWarps; wv++) {
+        const unsigned int c = s.whist[wv][tid];
+        s.whist[wv][tid] = dcount;
+        dcount += c;
+      }
+      incl = dcount;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+      }
+      if (lane == 31) s.wscan[warp] = incl;
+    }
+    __syncthreads();
+    if (tid < kRadix) {
+      unsigned int pre = 0;
+      for (int wv = 0; wv < warp; wv++) pre += s.wscan[wv];
+      s.dexcl[tid] = pre + incl - dcount;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < KPT; i++) {
+      if (wbase + i * 32 + lane < n) {
+        const unsigned int dg = (unsigned int)(w[i] >> shift) & 255u;
+        s.words[s.dexcl[dg] + s.whist[warp][dg] + rank[i]] = w[i];
+      }
+    }
+    __syncthreads();
+  }
+}
+
+__global__ void __launch_bounds__(kTileSortThreads, 2) tile_sort_gather_kernel(Workspace ws, int G,
+                                                                            const unsigned long long* __restrict__ pairs,
+                                                                            unsigned long long* __restrict__ keys_out,
+                                                                            unsigned int* __restrict__ vals_out) {
+  extern __shared__ __align__(16) unsigned char ts_raw[];
+  TileSortSmem& s = *reinterpret_cast<TileSortSmem*>(ts_raw);
   const int bid = ws.use_order ? (int)ws.tile_order[blockIdx.x] : (int)blockIdx.x;
   const uint2 r = ws.ranges[bid];
   const int n = (int)(r.y - r.x);
   if (n == 0 || n > kSmallTileCap) return;
   const int tid = threadIdx.x;
-  for (int i = tid; i < n; i += 256) s[i] = pairs[r.x + i];
+  for (int i = tid; i < n; i += kTileSortThreads) s.words[i] = pairs[r.x + i];
+  if (tid == 0) s.nruns = 0;
   __syncthreads();
-  bitonic_sort_words(s, n, tid, 256);
-  write_sorted_tile(ws, s, n, r.x, bid, G, keys_out, vals_out, tid, 256);
+  if (n <= 1 * kTileSortThreads) radix_sort_tile_by_depth<1>(s, n, tid);
+  else if (n <= 2 * kTileSortThreads) radix_sort_tile_by_depth<2>(s, n, tid);
+  else if (n <= 4 * kTileSortThreads) radix_sort_tile_by_depth<4>(s, n, tid);
+  else radix_sort_tile_by_depth<8>(s, n, tid);
+  // equal depths: the words of a run are still in emission (atomic) order; order them by Gaussian id
+  unsigned int* runs = &s.whist[0][0];  // free now: up to kTileSortWarps*kRadix = 4096 run starts
+  for (int i = tid; i + 1 < n; i += kTileSortThreads) {
+    const unsigned int d = (unsigned int)(s.words[i] >> 32);
+    if ((unsigned int)(s.words[i + 1] >> 32) == d && (i == 0 || (unsigned int)(s.words[i - 1] >> 32) != d))
+      runs[atomicAdd(&s.nruns, 1u)] = (unsigned int)i;
+  }
+  __syncthreads();
+  for (unsigned int k = tid; k < s.nruns; k += kTileSortThreads) {
+    const int b0 = (int)runs[k];
+    const unsigned int d = (unsigned int)(s.words[b0] >> 32);
+    int e = b0 + 1;
+    while (e < n && (unsigned int)(s.words[e] >> 32) == d) e++;
+    for (int i = b0 + 1; i < e; i++) {  // insertion sort of the run (whole words: same high half)
+      const unsigned long long x = s.words[i];
+      int j = i - 1;
+      while (j >= b0 && s.words[j] > x) { s.words[j + 1] = s.words[j]; j--; }
+      s.words[j + 1] = x;
+    }
+  }
+  __syncthreads();
+  write_sorted_tile(ws, s.words, n, r.x, bid, G, keys_out, vals_out, tid, kTileSortThreads);
 }
 
 // tiles above kSmallTileCap: a few persistent CTAs with a 128-KB buffer; above kBigTileCap in place in HBM
-__global__ void __launch_bounds__(1024) big_tile_sort_gather_kernel(Workspace ws, int G, unsigned long long* __restrict__ pairs,
+__global__ void __launch_bounds__(512) big_tile_sort_gather_kernel(Workspace ws, int G, unsigned long long* __restrict__ pairs,
                                                                     unsigned long long* __restrict__ keys_out,
                                                                     unsigned int* __restrict__ vals_out) {
   extern __shared__ __align__(16) unsigned long long sbig[];
@@ -238,15 +411,15 @@ __global__ void __launch_bounds__(1024) big_tile_sort_gather_kernel(Workspace ws
     const uint2 r = ws.ranges[bid];
     const int n = (int)(r.y - r.x);
     if (n <= kBigTileCap) {
-      for (int i = tid; i < n; i += 1024) sbig[i] = pairs[r.x + i];
+      for (int i = tid; i < n; i += 512) sbig[i] = pairs[r.x + i];
       __syncthreads();
-      bitonic_sort_words(sbig, n, tid, 1024);
-      write_sorted_tile(ws, sbig, n, r.x, bid, G, keys_out, vals_out, tid, 1024);
+      bitonic_sort_words(sbig, n, tid, 512);
+      write_sorted_tile(ws, sbig, n, r.x, bid, G, keys_out, vals_out, tid, 512);
     } else {
       unsigned long long* seg = pairs + r.x;  // this CTA is the only one that touches the segment
       __syncthreads();
-      bitonic_sort_words(seg, n, tid, 1024);
-      write_sorted_tile(ws, seg, n, r.x, bid, G, keys_out, vals_out, tid, 1024);
+      bitonic_sort_words(seg, n, tid, 512);
+      write_sorted_tile(ws, seg, n, r.x, bid, G, keys_out, vals_out, tid, 512);
     }
     __syncthreads();  // the buffer is reused by the next tile of this CTA
   }
@@ -271,13 +444,16 @@ cudaError_t launch_bucket_sort_gather(const TsplatProblem& p, const Workspace& w
   unsigned long long* keys_out = ws.keys[ws.sort_passes & 1];
   unsigned int* vals_out = ws.vals[ws.sort_passes & 1];
   const int NT = ws.N * ws.T;
-  tile_sort_gather_kernel<<<NT, 256, 0, st>>>(ws, p.G, pairs, keys_out, vals_out);
-  cudaError_t e = cudaGetLastError();
+  cudaError_t e = cudaFuncSetAttribute(tile_sort_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       (int)sizeof(TileSortSmem));
+  if (e != cudaSuccess) return e;
+  tile_sort_gather_kernel<<<NT, kTileSortThreads, sizeof(TileSortSmem), st>>>(ws, p.G, pairs, keys_out, vals_out);
+  e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const int smem = kBigTileCap * (int)sizeof(unsigned long long);
   e = cudaFuncSetAttribute(big_tile_sort_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
-  big_tile_sort_gather_kernel<<<148, 1024, smem, st>>>(ws, p.G, pairs, keys_out, vals_out);
+  big_tile_sort_gather_kernel<<<148, 512, smem, st>>>(ws, p.G, pairs, keys_out, vals_out);
   return cudaGetLastError();
 }
 

@@ -15,8 +15,7 @@ namespace tsplat {
 //   power = -q, q = (A dx^2 + C dy^2)/2 + B dx dy ; passes only if q <= tau = ln(255 o)
 //   => |dx| <= sqrt(2 tau C/det), |dy| <= sqrt(2 tau A/det), det = AC - B^2.
 // Margins: binary32 evaluation of q has relative error <= 12 eps kappa, kappa = AC/det (see
-// DESIGN.md); the fast exp adds ~1e-6 to tau; coordinates compare with +0.01 px.  Evaluated in
-// binary64 so that det itself carries no cancellation error.
+// DESIGN.md); the fast exp/log add ~1e-6 to tau; coordinates compare with +0.01 px.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ unsigned int pack_extent(float hx, float hy) {
   const unsigned int lo = __half_as_ushort(__float2half_ru(hx)), hi = __half_as_ushort(__float2half_ru(hy));
@@ -25,16 +24,18 @@ __device__ __forceinline__ unsigned int pack_extent(float hx, float hy) {
 __device__ __forceinline__ unsigned int cull_extent(float A, float B, float C, float o) {
   const float inf = __int_as_float(0x7f800000);
   if (o < 1.0f / 255.0f) return pack_extent(-inf, -inf);  // alpha <= o < 1/255 on every pixel
-  const double det = (double)A * (double)C - (double)B * (double)B;
-  if (!(det > 0.0) || !(A > 0.0f) || !(C > 0.0f)) return pack_extent(inf, inf);
-  const double kappa = ((double)A * (double)C) / det;
-  const double delta = 2e-6 * kappa;
-  if (!(delta < 0.5)) return pack_extent(inf, inf);
-  const double tau = (log(255.0 * (double)o) + 1e-4) * 1.002 / (1.0 - delta);
-  const double hx = sqrt(2.0 * tau * (double)C / det) + 0.01, hy = sqrt(2.0 * tau * (double)A / det) + 0.01;
-  float fx = (float)hx * 1.0001f, fy = (float)hy * 1.0001f;
-  if (!(fx == fx) || !(fy == fy)) return pack_extent(inf, inf);
-  return pack_extent(fx, fy);
+  // det in binary64 (the products are exact there, so det carries no cancellation error), the rest in
+  // binary32: its ~1e-6 relative error is far inside the 2e-3 margin on tau
+  const float det = (float)((double)A * (double)C - (double)B * (double)B);
+  if (!(det > 0.0f) || !(A > 0.0f) || !(C > 0.0f)) return pack_extent(inf, inf);
+  const float kappa = __fdividef(A * C, det);
+  const float delta = 2e-6f * kappa;
+  if (!(delta < 0.5f)) return pack_extent(inf, inf);
+  const float tau = (__logf(255.0f * o) + 2e-4f) * __fdividef(1.003f, 1.0f - delta);
+  const float s2 = __fdividef(2.0f * tau, det);
+  const float hx = sqrtf(s2 * C) * 1.0002f + 0.01f, hy = sqrtf(s2 * A) * 1.0002f + 0.01f;
+  if (!(hx == hx) || !(hy == hy)) return pack_extent(inf, inf);
+  return pack_extent(hx, hy);
 }
 
 }  // namespace tsplat
