@@ -227,7 +227,7 @@ def run_ours(args):
                    "api": "DecoderSplattingCUDA.forward(depth_mode='depth') + torch.autograd.grad"},
         "clocks": clocks,
         "e2e": e2e,
-        "gpu_launches": args.steps * (7 + sort_passes(VIEWS, T)),  # cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd, render bwd, preprocess bwd
+        "gpu_launches": args.steps * launches_per_step(VIEWS, T),
         "roofline": {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
                      "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": round(top_bytes), "kernel_ms": round(kern[top], 4),
@@ -242,6 +242,16 @@ def run_ours(args):
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
+
+
+def launches_per_step(n_views: int, T: int) -> int:
+    """Kernels of libtsplat.so launched per step (the two torch elementwise kernels of the MSE gradient are not ours).
+    bucket path (default): pack_cameras, preprocess_forward, bucket_scan, bucket_emit, tile_sort_gather,
+    big_tile_sort_gather, render_forward, render_backward, preprocess_backward = 9;
+    onesweep path: pack_cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd/bwd, preprocess bwd."""
+    if os.environ.get("TSPLAT_SORT", "bucket") == "onesweep":
+        return 7 + sort_passes(n_views, T)
+    return 9
 
 
 def sort_passes(n_views: int, T: int) -> int:

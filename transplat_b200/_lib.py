@@ -7,7 +7,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libtsplat.so")
+# TSPLAT_LIB_PATH: development only (kernel experiments built with `make OUT=... EXTRA=-D...`)
+LIB_PATH = os.environ.get("TSPLAT_LIB_PATH") or os.path.join(_HERE, "lib", "libtsplat.so")
 CSRC = os.path.join(_HERE, "csrc")
 
 TSPLAT_OK, TSPLAT_EINVAL, TSPLAT_ENOSPC, TSPLAT_ECUDA = 0, 1, 2, 3

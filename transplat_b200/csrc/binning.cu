@@ -349,7 +349,7 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
     const float4 f = ws.rgbd[o];
     ws.rec0[j] = make_float4(c.x, c.y, co.x, co.y);
     ws.rec1[j] = make_float4(co.z, co.w, f.x, f.y);
-    ws.rec2[j] = make_float4(f.z, f.w, __uint_as_float(id), __uint_as_float(cull_extent(co.x, co.y, co.z, co.w)));
+    ws.rec2[j] = make_float4(f.z, f.w, __uint_as_float(id), cull_tau(co.x, co.y, co.z, co.w));
   }
   if (!ws.use_order) return;
   // The last CTA to finish orders the (view, tile) ids by list length, longest first (counting sort

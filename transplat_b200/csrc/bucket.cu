@@ -262,7 +262,7 @@ __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const uns
         ws.rec0[start + j] = make_float4(c[u].x, c[u].y, co[u].x, co[u].y);
         ws.rec1[start + j] = make_float4(co[u].z, co[u].w, f[u].x, f[u].y);
         ws.rec2[start + j] = make_float4(f[u].z, f[u].w, __uint_as_float(id),
-                                         __uint_as_float(cull_extent(co[u].x, co[u].y, co[u].z, co[u].w)));
+                                         cull_tau(co[u].x, co[u].y, co[u].z, co[u].w));
       }
     }
   }

@@ -142,6 +142,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   while (!mbar_try_wait(bar, parity)) {
   }
 }
+// (Measured on B200: replacing this hardware-assisted wait by test_wait + __nanosleep back-off removes the
+// TRYWAIT/NANOSLEEP.SYNCS loop instructions - 17 % of the render kernels' issued instructions - but does not
+// shorten the kernels: those issue slots were idle anyway; profiles/r01_experiments.md.)
 // global -> shared::cta bulk copy; bytes % 16 == 0, both addresses 16-B aligned.
 __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
   asm volatile(

@@ -6,7 +6,7 @@
 // kStages stages x kStageEntries entries by a dedicated producer warp with 1-D TMA bulk copies
 // (cp.async.bulk -> mbarrier complete_tx).  The 8 consumer warps (one 8x4 pixel block each) run
 // DECOUPLED: each waits on a stage's `full` barrier, culls the stage's entries against its own
-// pixel block (conservative extents, exact in effect), composites the survivors, and arrives on the
+// pixel block (minimum of the quadratic over the block, exact in effect), composites the survivors, and arrives on the
 // stage's `empty` barrier; the producer refills a stage once all 8 warps have released it.  Depth
 // order makes consecutive entries spatially clustered, so per-batch CTA-wide barriers left warps
 // idle ~40% of the time; the ring lets them drift up to kStages-1 stages apart.
@@ -26,7 +26,7 @@ constexpr int kRenderThreads = kTilePix + 32;     // + the producer warp
 struct RingSmem {
   float4 r0[kStages][kStageEntries];  // x, y, conic.x, conic.y
   float4 r1[kStages][kStageEntries];  // conic.z, opacity, r, g
-  float4 r2[kStages][kStageEntries];  // b, depth feature, bits(Gaussian id), packed fp16 extents
+  float4 r2[kStages][kStageEntries];  // b, depth feature, bits(Gaussian id), cull threshold tau_s
   uint64_t full[kStages];
   uint64_t empty[kStages];
   int done_warps;
@@ -60,18 +60,29 @@ __device__ __forceinline__ void pixel_of_thread(int tid, int& bx, int& by, int& 
   lx = lane & 7; ly = lane >> 3;
 }
 
-// Per-warp culling: bit l of the result is set iff entry j (one per lane) can touch the warp's
-// block [X0, X0+7] x [Y0, Y0+3] according to the conservative extents packed in rec2.w
-// (cull_extent, binning.cu).
-__device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0, const float4* __restrict__ r2,
-                                                   int j, bool in_range, float X0, float Y0) {
+// Per-warp culling: bit l of the result is set iff entry j (one per lane) can pass the alpha test on some
+// pixel of the warp's block [X0, X0+7] x [Y0, Y0+3].  Exact in the continuous sense: the minimum of
+//   q(dx, dy) = (A dx^2 + C dy^2)/2 + B dx dy      (power = -q)
+// over the rectangle is compared with tau_s (rec2.w, cull_tau in cull.cuh).  q is convex with its
+// minimum at the centre, so over a box that does not contain the centre the minimum lies on an edge
+// facing it: with (ax, by) the box point nearest the centre per axis, the candidates are the 1-D minima
+// along dx = ax and along dy = by (if the centre is inside, both are 0).  Evaluating q at a slightly
+// different point of the box can only over-estimate the minimum by O(eps^2 q kappa), inside the margin.
+__device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0, const float4* __restrict__ r1,
+                                                   const float4* __restrict__ r2, int j, bool in_range, float X0,
+                                                   float Y0) {
   bool hit = false;
   if (in_range) {
-    const float2 c = *reinterpret_cast<const float2*>(&r0[j]);
-    const unsigned int e = __float_as_uint(r2[j].w);
-    const float hx = __half2float(__ushort_as_half((unsigned short)(e & 0xffffu)));
-    const float hy = __half2float(__ushort_as_half((unsigned short)(e >> 16)));
-    hit = (c.x + hx >= X0) && (c.x - hx <= X0 + 7.0f) && (c.y + hy >= Y0) && (c.y - hy <= Y0 + 3.0f);
+    const float4 a0 = r0[j];     // x, y, A, B
+    const float Cq = r1[j].x;    // C
+    const float tau = r2[j].w;
+    const float a_lo = X0 - a0.x, a_hi = a_lo + 7.0f, b_lo = Y0 - a0.y, b_hi = b_lo + 3.0f;
+    const float ax = fminf(fmaxf(0.0f, a_lo), a_hi), by = fminf(fmaxf(0.0f, b_lo), b_hi);
+    const float dy1 = fminf(fmaxf(__fdividef(-a0.w * ax, Cq), b_lo), b_hi);
+    const float dx2 = fminf(fmaxf(__fdividef(-a0.w * by, a0.z), a_lo), a_hi);
+    const float q1 = 0.5f * (a0.z * ax * ax + Cq * dy1 * dy1) + a0.w * ax * dy1;
+    const float q2 = 0.5f * (a0.z * dx2 * dx2 + Cq * by * by) + a0.w * dx2 * by;
+    hit = !(fminf(q1, q2) > tau);  // NaN (degenerate conic) => keep
   }
   return __ballot_sync(0xffffffffu, hit);
 }
@@ -158,7 +169,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
       unsigned int mask[kStageEntries / 32];
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++)
-        mask[i] = cull_round(r0, r2, i * 32 + lane, i * 32 + lane < cnt, X0, Y0);
+        mask[i] = cull_round(r0, r1, r2, i * 32 + lane, i * 32 + lane < cnt, X0, Y0);
       const unsigned int base = (unsigned int)(b * kStageEntries) + 1u;  // 1-based list position of entry 0
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++) {
@@ -307,9 +318,14 @@ __device__ __forceinline__ void flush_stage(RingBwdSmem& s, int st, int cnt, int
                        (q1.y != 0.0f) | (q1.z != 0.0f) | (q1.w != 0.0f) | (q2.x != 0.0f) | (q2.y != 0.0f);
       if (any) {
         float* dst = grad_acc + (view_base + id) * kAccFloats;
-        red_add_v4(dst, q0.x, q0.y, q0.z, q0.w);
-        red_add_v4(dst + 4, q1.x, q1.y, q1.z, q1.w);
-        red_add_v4(dst + 8, q2.x, q2.y, 0.0f, 0.0f);
+#ifdef TSPLAT_EXP_NOFLUSH
+        if (q0.x == 123.456f)
+#endif
+        {
+          red_add_v4(dst, q0.x, q0.y, q0.z, q0.w);
+          red_add_v4(dst + 4, q1.x, q1.y, q1.z, q1.w);
+          red_add_v4(dst + 8, q2.x, q2.y, 0.0f, 0.0f);
+        }
         const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
         a4[0] = z; a4[1] = z; a4[2] = z;
       }
@@ -410,7 +426,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++) {
         const int j = i * 32 + lane;
-        mask[i] = cull_round(r0, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
+        mask[i] = cull_round(r0, r1, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
       }
 #pragma unroll
       for (int i = kStageEntries / 32 - 1; i >= 0; i--) {
@@ -460,8 +476,16 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
             v[4] = -0.5f * gdy * dy * dL_dG;
             v[5] = Gv * dL_dalpha;
           }
+#ifdef TSPLAT_EXP_NOREDUCE
+          if (v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7] + v[8] + v[9] == 123.456f) s.acc[st][j][0] = 1.0f;
+#else
           const float r = warp_transpose_reduce10(v, lane);
+#ifdef TSPLAT_EXP_NOATOM
+          if (r == 123.456f) s.acc[st][j][0] = 1.0f;
+#else
           if (my_red) atomicAdd(&s.acc[st][j][my_comp], r);
+#endif
+#endif
         }
       }
     }

@@ -25,6 +25,7 @@ class HostPipeline:
         self._dev_in = [None] * slots      # per-slot device input buffers (allocated once per shape)
         self._keep = [None] * slots        # per-slot outputs kept alive until their D2H has finished
         self._done = [None] * slots        # per-slot event: D2H of the step that last used the slot
+        self._computed = [None] * slots    # per-slot event: kernels of the step that last used the slot
         self._i = 0
 
     def _buffers(self, k: int, host_in: Dict[str, torch.Tensor]):
@@ -44,6 +45,10 @@ class HostPipeline:
         if self._done[k] is not None:
             self._done[k].synchronize()  # back-pressure: the slot's previous step has fully drained
         dev = self._buffers(k, host_in)
+        # only THIS slot's previous compute must have finished before its inputs are overwritten; the other
+        # slots' kernels keep running under this copy (a stream-wide wait would serialise copy and compute)
+        if self._computed[k] is not None:
+            self.h2d.wait_event(self._computed[k])
         with torch.cuda.stream(self.h2d):
             for n, t in host_in.items():
                 dev[n].copy_(t, non_blocking=True)
@@ -59,8 +64,7 @@ class HostPipeline:
                 h.copy_(out[n].detach(), non_blocking=True)
             ev_out = torch.cuda.Event()
             ev_out.record(self.d2h)
-        # the H2D stream must not overwrite this slot's inputs before the compute that reads them is done
-        self.h2d.wait_event(ev_c)
+        self._computed[k] = ev_c
         self._keep[k] = out
         self._done[k] = ev_out
         return ev_out
