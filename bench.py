@@ -247,11 +247,11 @@ def run_ours(args):
 def launches_per_step(n_views: int, T: int) -> int:
     """Kernels of libtsplat.so launched per step (the two torch elementwise kernels of the MSE gradient are not ours).
     bucket path (default): pack_cameras, preprocess_forward, bucket_scan, bucket_emit, tile_sort_gather,
-    big_tile_sort_gather, render_forward, render_backward, preprocess_backward = 9;
+    big_tile_sort_gather, render_forward, status_store, render_backward, preprocess_backward = 10;
     onesweep path: pack_cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd/bwd, preprocess bwd."""
     if os.environ.get("TSPLAT_SORT", "bucket") == "onesweep":
-        return 7 + sort_passes(n_views, T)
-    return 9
+        return 8 + sort_passes(n_views, T)
+    return 10
 
 
 def sort_passes(n_views: int, T: int) -> int:
@@ -279,27 +279,36 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
     from transplat_b200.decoder import Gaussians
     from transplat_b200.streaming import HostPipeline
 
-    pin = lambda t: t.contiguous().pin_memory()
-    host = [dict(means=pin(s.means[None]), cov=pin(s.covariances[None]), sh=pin(s.harmonics[None]),
-                 op=pin(s.opacities[None]), ext=pin(s.extrinsics[None]), intr=pin(s.intrinsics[None]),
-                 near=pin(s.near[None]), far=pin(s.far[None]), target=pin(target_h[None]), dLd=pin(dLd_h[None]))
-            for s in scenes]
+    from transplat_b200.rasterize import flat_gradients, flat_images
+    from transplat_b200.streaming import SlabLayout
+
     G = scenes[0].means.shape[0]
+    # one pinned slab per scene for the inputs, two per result set (images, gradients): a step crosses PCIe as
+    # one H2D and two D2H copies (scripts/pcie_bw.py: 16 separate tensor copies cost 20 % more for the same bytes)
+    lay_in = SlabLayout(dict(means=(1, G, 3), cov=(1, G, 3, 3), sh=(1, G, 3, 25), op=(1, G), ext=(1, VIEWS, 4, 4),
+                             intr=(1, VIEWS, 3, 3), near=(1, VIEWS), far=(1, VIEWS), target=(1, VIEWS, 3, HW, HW),
+                             dLd=(1, VIEWS, HW, HW)))
+    host = [dict(slab=lay_in.pack_pinned(dict(
+        means=s.means[None], cov=s.covariances[None], sh=s.harmonics[None], op=s.opacities[None], ext=s.extrinsics[None],
+        intr=s.intrinsics[None], near=s.near[None], far=s.far[None], target=target_h[None], dLd=dLd_h[None])))
+        for s in scenes]
+    lay_img = SlabLayout(dict(color=(1, VIEWS, 3, HW, HW), depth=(1, VIEWS, HW, HW)))
+    lay_grad = SlabLayout(dict(g_means=(1, G, 3), g_cov=(1, G, 3, 3), g_sh=(1, G, 3, 25), g_op=(1, G)))
     n_out = 4  # result buffers cycled (a consumer would read them between steps)
-    outs = [dict(color=torch.empty((1, VIEWS, 3, HW, HW)).pin_memory(), depth=torch.empty((1, VIEWS, HW, HW)).pin_memory(),
-                 g_means=torch.empty((1, G, 3)).pin_memory(), g_cov=torch.empty((1, G, 3, 3)).pin_memory(),
-                 g_sh=torch.empty((1, G, 3, 25)).pin_memory(), g_op=torch.empty((1, G)).pin_memory())
-            for _ in range(n_out)]
+    outs = [dict(images=lay_img.empty_pinned(), grads=lay_grad.empty_pinned()) for _ in range(n_out)]
     numel = float(VIEWS * 3 * HW * HW)
-    h2d = sum(t.numel() * 4 for t in host[0].values())
+    h2d = host[0]["slab"].numel() * 4
     d2h = sum(t.numel() * 4 for t in outs[0].values())
 
-    def step_fn(d):
+    def step_fn(dv):
+        d = lay_in.views(dv["slab"])
         leaves = [d[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
         out = decoder.forward(Gaussians(*leaves), d["ext"], d["intr"], d["near"], d["far"], (HW, HW), depth_mode="depth")
         dLc = (out.color - d["target"]) * (2.0 / numel)
         g = torch.autograd.grad([out.color, out.depth], leaves, [dLc, d["dLd"]])
-        return dict(color=out.color, depth=out.depth, g_means=g[0], g_cov=g[1], g_sh=g[2], g_op=g[3])
+        images, grads = flat_images(out.color, out.depth), flat_gradients(*g)
+        assert images is not None and images.numel() == lay_img.total and grads.numel() == lay_grad.total
+        return dict(images=images, grads=grads)
 
     pipe = HostPipeline(dev, slots=3)
     steps = max(10, min(args.steps, 100))
@@ -322,7 +331,8 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
     ms /= steps
     return {"value": round(world * VIEWS / (ms * 1e-3), 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms, 4), "steps": steps,
-            "how": "pinned host inputs -> H2D stream -> kernels -> D2H stream -> pinned host results, 3 slots in flight; "
+            "how": "pinned host slab (Gaussians, cameras, target) -> H2D stream -> kernels -> D2H stream -> pinned host "
+                   "slabs (colour+depth, all four gradients), 3 slots in flight; "
                    f"{N_SCENES} scenes x {h2d >> 20} MiB cycled (> L2), window timed with CUDA events"}
 
 

@@ -186,7 +186,10 @@ int tsplat_pack_cameras(int32_t N, const float* extrinsics, const float* intrins
                         int32_t bg_stride, int32_t scale_invariant, TsplatCamera* cams,
                         void* cuda_stream);
 
-/* Copies the status block to pinned/pageable host memory asynchronously on the stream. */
+/* Copies the status block to host memory asynchronously on the stream.  status_host should be pinned
+ * (cudaHostAlloc / cudaHostRegister, 16-byte aligned): it is then written by a one-warp kernel through its
+ * device alias, so the read never queues on a copy engine behind another stream's bulk transfer; pageable
+ * memory falls back to cudaMemcpyAsync. */
 int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream);
 
 /* Optional per-stage device timing (cudaEvents recorded on the caller's stream around each stage;

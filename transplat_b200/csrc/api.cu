@@ -336,8 +336,19 @@ int tsplat_profile_read(float* ms_host, int n) {
 
 int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream) {
   if (!workspace || !status_host) { set_error("bad status_read arguments"); return TSPLAT_EINVAL; }
-  cudaError_t e = cudaMemcpyAsync(status_host, workspace, sizeof(TsplatStatus), cudaMemcpyDeviceToHost,
-                                  static_cast<cudaStream_t>(cuda_stream));
+  cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
+  // Pinned (or registered) host memory is written by a one-warp kernel through its device alias: a 16-byte
+  // cudaMemcpyAsync would go through a copy engine and queue behind whatever bulk D2H transfer another stream
+  // has in flight there (measured: it stalled the backward kernels ~0.7 ms per step in the host-buffer pipeline).
+  cudaPointerAttributes attr;
+  cudaError_t e = cudaPointerGetAttributes(&attr, status_host);
+  if (e == cudaSuccess && attr.type == cudaMemoryTypeHost && attr.devicePointer != nullptr) {
+    tsplat::launch_status_store(workspace, attr.devicePointer, st);
+    e = cudaGetLastError();
+  } else {
+    (void)cudaGetLastError();  // pageable memory: clear the attribute query's error, fall back to a copy
+    e = cudaMemcpyAsync(status_host, workspace, sizeof(TsplatStatus), cudaMemcpyDeviceToHost, st);
+  }
   if (e != cudaSuccess) return cuda_fail("status_read", e);
   return TSPLAT_OK;
 }

@@ -175,4 +175,15 @@ cudaError_t launch_pack_cameras(int N, const float* extrinsics, const float* int
   return cudaGetLastError();
 }
 
+// 16-byte status block -> pinned host memory through its device alias (tsplat_status_read)
+__global__ void status_store_kernel(const uint4* __restrict__ status, uint4* host_alias) {
+  if (threadIdx.x == 0) {
+    *host_alias = *status;
+    __threadfence_system();
+  }
+}
+void launch_status_store(const void* workspace, void* host_alias, cudaStream_t st) {
+  status_store_kernel<<<1, 32, 0, st>>>(static_cast<const uint4*>(workspace), static_cast<uint4*>(host_alias));
+}
+
 }  // namespace tsplat

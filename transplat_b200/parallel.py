@@ -37,6 +37,13 @@ class _SumGradsAcrossRanks(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, *grads):
+        # the rasterizer's backward returns its four gradients as views of one flat slab: reduce it in place
+        # (no packing copy); anything else is packed first
+        from .rasterize import flat_gradients
+        base = flat_gradients(*grads)
+        if base is not None and base.is_contiguous():
+            dist.all_reduce(base, op=dist.ReduceOp.SUM, group=ctx.group)
+            return (None, *grads)
         shapes = [g.shape for g in grads]
         sizes = [g.numel() for g in grads]
         slab = torch.empty(sum(sizes), dtype=grads[0].dtype, device=grads[0].device)

@@ -173,8 +173,11 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
             layout = TsplatLayout()
             _lib.check(L.tsplat_workspace_layout(C.byref(prob), d_cap, C.byref(layout)), "tsplat_workspace_layout")
             ws = torch.empty(layout.total_bytes, dtype=torch.uint8, device=dev)
-            color = torch.empty((N, 3, cfg.H, cfg.W), dtype=torch.float32, device=dev)
-            depth = torch.empty((N, cfg.H, cfg.W), dtype=torch.float32, device=dev) if cfg.depth_mode else None
+            # colour and depth share one flat allocation (one D2H copy for a caller that wants both on the host)
+            n_col, n_dep = N * 3 * cfg.H * cfg.W, (N * cfg.H * cfg.W if cfg.depth_mode else 0)
+            images = torch.empty(_pad64(n_col) + n_dep, dtype=torch.float32, device=dev)
+            color = images[:n_col].view(N, 3, cfg.H, cfg.W)
+            depth = images[_pad64(n_col):_pad64(n_col) + n_dep].view(N, cfg.H, cfg.W) if cfg.depth_mode else None
             radii = torch.empty((N, G), dtype=torch.int32, device=dev) if cfg.want_radii else None
             _lib.check(L.tsplat_forward(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
                                         _ptr(depth), _ptr(radii), C.c_void_p(stream.cuda_stream)),
@@ -237,10 +240,16 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
                 (N, cfg.H, cfg.W), dtype=torch.float32, device=dev)
         else:
             grad_depth = None
-        g_means = torch.empty_like(means)
-        g_cov = torch.empty_like(cov)
-        g_sh = torch.empty_like(sh)
-        g_op = torch.empty_like(opacity)
+        # the four per-Gaussian gradients are views of ONE flat slab [means | cov | sh | opacity] (segments
+        # 256-B aligned): a view-sharded caller all-reduces it in place (parallel.py), a host-side caller
+        # copies it back with one transfer (flat_gradients below)
+        sizes = [means.numel(), cov.numel(), sh.numel(), opacity.numel()]
+        offs = [0]
+        for n_ in sizes[:-1]:
+            offs.append(offs[-1] + _pad64(n_))
+        slab = torch.empty(offs[-1] + sizes[-1], dtype=torch.float32, device=dev)
+        g_means, g_cov, g_sh, g_op = (slab[o:o + n_].view(t.shape)
+                                      for o, n_, t in zip(offs, sizes, (means, cov, sh, opacity)))
         g_m2d = (torch.empty((N, means.shape[1], 3), dtype=torch.float32, device=dev)
                  if cfg.want_means2d_grad else None)
         # the forward leaves the screen-space accumulators zero; every further backward re-clears them
@@ -277,6 +286,26 @@ class _Rasterize(torch.autograd.Function):
         if ctx.has_m2d and g_m2d is not None:
             g_m2d = g_m2d.reshape(ctx.m2d_shape)
         return g_means, g_cov, g_sh, g_op, (g_m2d if ctx.has_m2d else None), None, None
+
+
+def _pad64(n: int) -> int:
+    return (n + 63) // 64 * 64
+
+
+def flat_gradients(*grads):
+    """The flat slab the gradients returned by one backward call are views of (None if they are not)."""
+    base = getattr(grads[0], "_base", None)
+    if base is None or any(getattr(g, "_base", None) is not base for g in grads):
+        return None
+    return base
+
+
+def flat_images(color, depth=None):
+    """The flat slab colour (and depth) of one forward call are views of (None if they are not)."""
+    base = getattr(color, "_base", None)
+    while base is not None and getattr(base, "_base", None) is not None:
+        base = base._base
+    return base
 
 
 def rasterize(means, cov, sh, opacity, cams, cfg: RenderConfig, means2d=None):
