@@ -246,3 +246,92 @@ def test_host_pipeline_matches_direct_call():
         for k in o:
             w = want[k].detach().cpu()
             assert float((o[k] - w).abs().max()) <= 1e-5 * float(w.abs().max()) + 1e-7, k
+
+
+# ------------------------------------------------------------------------------------------------
+# remaining call-surface variants against tests/golden/ref_host_variants.npz, made by the
+# unmodified reference host code (tests/golden/make_golden_variants.py)
+# ------------------------------------------------------------------------------------------------
+GOLD_VAR = os.path.join(ROOT, "tests", "golden", "ref_host_variants.npz")
+
+
+def _gold_var():
+    z, t = _gold()
+    zv = np.load(GOLD_VAR)
+    return z, t, zv, (lambda k: torch.from_numpy(zv[k]).cuda())
+
+
+def _rel(got, want):
+    want = np.asarray(want, np.float64)
+    return np.abs(got.detach().cpu().numpy() - want).max() / max(np.abs(want).max(), 1e-30)
+
+
+def test_golden_render_cuda_with_stats():
+    from transplat_b200 import decoder as D
+    z, t, zv, tv = _gold_var()
+    H, W = z["color"].shape[-2:]
+    V = z["extrinsics"].shape[0]
+    rep = lambda k: t(k)[None].expand(V, *z[k].shape)
+    img, stats = D.render_cuda_with_stats(t("extrinsics"), t("intrinsics"), t("near"), t("far"), (H, W),
+                                          t("bg")[None].expand(V, 3), rep("means"), rep("cov"), rep("harmonics"),
+                                          rep("opacities"), opacity_threshold=0.3)
+    assert np.abs(img.cpu().numpy() - zv["stats_color"]).max() <= COLOR_ATOL
+    assert [s.visible_gaussians for s in stats] == zv["stats_visible"].tolist()
+    assert [s.high_contribution_gaussians for s in stats] == zv["stats_high"].tolist()
+    for i, s in enumerate(stats):
+        assert s.total_gaussians == z["means"].shape[0] and s.opacity_threshold == 0.3
+        assert np.array_equal(s.radii.cpu().numpy(), zv["stats_radii"][i])  # radii bit-exact
+    # the decoder method returns the same statistics, one per (scene, view)
+    dec = D.DecoderSplattingCUDA(background_color=tuple(z["bg"].tolist())).cuda()
+    g = D.Gaussians(*(t(k)[None] for k in ("means", "cov", "harmonics", "opacities")))
+    out, stats2 = dec.forward_with_gaussian_stats(g, t("extrinsics")[None], t("intrinsics")[None], t("near")[None],
+                                                  t("far")[None], (H, W), depth_mode="depth", opacity_threshold=0.3)
+    assert [s.high_contribution_gaussians for s in stats2] == zv["stats_high"].tolist()
+    assert np.abs(out.depth[0].cpu().numpy() - z["depth_depth"]).max() <= COLOR_ATOL
+
+
+def test_golden_render_cuda_precomputed_colors():
+    """use_sh=False: colors_precomp = shs[:, 0, :] (cuda_splatting.py:130), forward and gradients."""
+    from transplat_b200 import decoder as D
+    z, t, zv, tv = _gold_var()
+    H, W = z["color"].shape[-2:]
+    V = z["extrinsics"].shape[0]
+    leaves = [x.clone().requires_grad_(True) for x in (t("means"), t("cov"), tv("precomp_colors"), t("opacities"))]
+    rep = lambda x: x[None].expand(V, *x.shape)
+    img = D.render_cuda(t("extrinsics"), t("intrinsics"), t("near"), t("far"), (H, W), t("bg")[None].expand(V, 3),
+                        rep(leaves[0]), rep(leaves[1]), rep(leaves[2]), rep(leaves[3]), use_sh=False)
+    assert np.abs(img.detach().cpu().numpy() - zv["precomp_color"]).max() <= COLOR_ATOL
+    (img * tv("precomp_w")).sum().backward()
+    for leaf, k in zip(leaves, ("precomp_g_means", "precomp_g_cov", "precomp_g_col", "precomp_g_op")):
+        assert _rel(leaf.grad, zv[k]) <= GRAD_RTOL, k
+
+
+def test_golden_render_cuda_orthographic():
+    from transplat_b200 import decoder as D
+    z, t, zv, tv = _gold_var()
+    H, W = z["color"].shape[-2:]
+    V = z["extrinsics"].shape[0]
+    leaves = [x.clone().requires_grad_(True) for x in (t("means"), t("cov"), t("harmonics"), t("opacities"))]
+    rep = lambda x: x[None].expand(V, *x.shape)
+    dump = {}
+    # one batched call for both views (the reference needs one call per view: its move_back is a single 4x4)
+    img = D.render_cuda_orthographic(t("extrinsics"), tv("ortho_width").expand(V), tv("ortho_height").expand(V),
+                                     tv("ortho_near").expand(V), tv("ortho_far").expand(V), (H, W),
+                                     t("bg")[None].expand(V, 3), rep(leaves[0]), rep(leaves[1]), rep(leaves[2]),
+                                     rep(leaves[3]), fov_degrees=0.1, dump=dump)
+    assert np.abs(img.detach().cpu().numpy() - zv["ortho_color"]).max() <= COLOR_ATOL
+    assert np.abs(dump["extrinsics"][V - 1].cpu().numpy() - zv["ortho_dump_extrinsics"][0]).max() <= 1e-3  # ~1.7e3 far
+    assert abs(float(dump["fov_y"][0]) - float(zv["ortho_dump_fov_y"][0])) <= 1e-9
+    (img * tv("ortho_w")).sum().backward()
+    for leaf, k in zip(leaves, ("ortho_g_means", "ortho_g_cov", "ortho_g_sh", "ortho_g_op")):
+        assert _rel(leaf.grad, zv[k].astype(np.float64).sum(0)) <= GRAD_RTOL, k
+
+
+def test_golden_mark_visible():
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    z, t, zv, tv = _gold_var()
+    vm = tv("visible_viewmatrix")
+    s = GaussianRasterizationSettings(32, 32, 0.5, 0.5, torch.zeros(3).cuda(), 1.0, vm, vm, 0, torch.zeros(3).cuda(),
+                                      False, False)
+    got = GaussianRasterizer(s).markVisible(t("means")).cpu().numpy().astype(np.uint8)
+    assert np.array_equal(got, zv["visible_view0"])

@@ -153,3 +153,25 @@ def pack_camera_from_settings(viewmatrix: Tensor, projmatrix: Tensor, campos: Te
     cam[0, O_TANX:] = tail.to(dev, non_blocking=True)
     cam[0, O_BG:O_BG + 3] = bg.reshape(3)
     return cam
+
+
+def pack_cameras_explicit(view_matrix: Tensor, full_projection: Tensor, campos: Tensor, tan_fov_x: Tensor,
+                          tan_fov_y: Tensor, background_color: Tensor) -> Tensor:
+    """[N] records from explicit matrices in the reference's transposed convention (what it passes as
+    ``viewmatrix`` / ``projmatrix``), no scale invariance: the camera set-up of render_cuda_orthographic
+    (cuda_splatting.py:165-214).  Everything stays on the device (tan_fov as tensors, no ``.item()``)."""
+    n = view_matrix.shape[0]
+    dev = view_matrix.device
+    cams = torch.zeros((n, CAM_FLOATS), dtype=torch.float32, device=dev)
+    cams[:, O_VIEW:O_VIEW + 16] = view_matrix.reshape(n, 16)
+    cams[:, O_PROJ:O_PROJ + 16] = full_projection.reshape(n, 16)
+    cams[:, O_CAMPOS:O_CAMPOS + 3] = campos.reshape(n, 3)
+    cams[:, O_TANX] = tan_fov_x
+    cams[:, O_TANY] = tan_fov_y
+    cams[:, O_BG:O_BG + 3] = background_color
+    cams[:, O_MSCALE] = 1.0
+    cams[:, O_CSCALE] = 1.0
+    cams[:, O_DROW + 2] = 1.0
+    cams[:, O_NEAR] = 1.0
+    cams[:, O_FAR] = 100.0
+    return cams

@@ -5,6 +5,7 @@ signatures and error behaviour
   DecoderOutput, DepthRenderingMode src/model/decoder/decoder.py:12-22
   render_cuda                       src/model/decoder/cuda_splatting.py:56-136
   render_depth_cuda                 src/model/decoder/cuda_splatting.py:375-417
+  render_cuda_orthographic          src/model/decoder/cuda_splatting.py:139-229
   render_cuda_with_stats            src/model/decoder/cuda_splatting.py:235-372
   DecoderSplattingCUDA              src/model/decoder/decoder_splatting_cuda.py:26-146
   DECODERS / get_decoder            src/model/decoder/__init__.py:5-13
@@ -25,7 +26,7 @@ import torch
 from torch import Tensor, nn
 
 from ._lib import COV_FULL9, DEPTH_MODES, SH_G3M
-from .cameras import pack_cameras_device
+from .cameras import _inverse, get_projection_matrix, pack_cameras_device, pack_cameras_explicit
 from .rasterize import RenderConfig, rasterize
 
 DepthRenderingMode = Literal["depth", "log", "disparity", "relative_disparity"]
@@ -59,7 +60,8 @@ class GaussianContributionStats:
 
 def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
                  image_shape: tuple, background_color: Tensor, depth_mode: Optional[str] = None,
-                 scale_invariant: bool = True, want_radii: bool = False, check: Optional[str] = None):
+                 scale_invariant: bool = True, want_radii: bool = False, check: Optional[str] = None,
+                 use_sh: bool = True, cams: Optional[Tensor] = None):
     """The batched entry point.  extrinsics [b,v,4,4], intrinsics [b,v,3,3], near/far [b,v],
     background_color [3] or [b*v,3].  Returns colour [b,v,3,h,w], depth [b,v,h,w]|None, radii [b,v,G]|None."""
     b, v = extrinsics.shape[:2]
@@ -68,13 +70,16 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
         raise ValueError(f"unknown depth_mode {depth_mode!r}")
     d_sh = gaussians.harmonics.shape[-1]
     degree = isqrt(d_sh) - 1
-    cams = pack_cameras_device(extrinsics.reshape(b * v, 4, 4), intrinsics.reshape(b * v, 3, 3),
-                               near.reshape(b * v), far.reshape(b * v), background_color,
-                               scale_invariant=scale_invariant)
+    assert use_sh or d_sh == 1  # cuda_splatting.py:70
+    if cams is None:
+        cams = pack_cameras_device(extrinsics.reshape(b * v, 4, 4), intrinsics.reshape(b * v, 3, 3),
+                                   near.reshape(b * v), far.reshape(b * v), background_color,
+                                   scale_invariant=scale_invariant)
     cfg = RenderConfig(H=h, W=w, V=v, sh_degree=degree, sh_layout=SH_G3M, cov_layout=COV_FULL9,
                        depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check)
-    color, depth, radii = rasterize(gaussians.means, gaussians.covariances, gaussians.harmonics,
-                                    gaussians.opacities, cams, cfg)
+    # use_sh=False: the single coefficient is the colour itself (colors_precomp = shs[:, 0, :], cuda_splatting.py:130)
+    feat = gaussians.harmonics if use_sh else gaussians.harmonics[..., 0]
+    color, depth, radii = rasterize(gaussians.means, gaussians.covariances, feat, gaussians.opacities, cams, cfg)
     color = color.reshape(b, v, 3, h, w)
     depth = depth.reshape(b, v, h, w) if depth is not None else None
     radii = radii.reshape(b, v, -1) if radii is not None else None
@@ -90,11 +95,75 @@ def render_cuda(extrinsics, intrinsics, near, far, image_shape, background_color
     assert use_sh or gaussian_sh_coefficients.shape[-1] == 1
     b = extrinsics.shape[0]
     g = Gaussians(gaussian_means, gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities)
-    if not use_sh:
-        raise NotImplementedError("use_sh=False: pass colours as degree-0 harmonics instead")
     color, _, _ = render_views(g, extrinsics[:, None], intrinsics[:, None], near[:, None], far[:, None],
-                               image_shape, background_color, None, scale_invariant)
+                               image_shape, background_color, None, scale_invariant, use_sh=use_sh)
     return color.reshape(b, 3, *image_shape)
+
+
+def render_cuda_orthographic(extrinsics, width, height, near, far, image_shape, background_color, gaussian_means,
+                             gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities,
+                             fov_degrees: float = 0.1, use_sh: bool = True, dump: Optional[dict] = None) -> Tensor:
+    """Signature and camera arithmetic of cuda_splatting.py:139-229: a "fake orthographic" camera pulled back
+    until ``fov_degrees`` spans ``width``.  The reference writes a [batch] distance into ONE 4x4 ``move_back``
+    (:169-170), which only works for batch 1; here each batch entry gets its own."""
+    b = extrinsics.shape[0]
+    assert use_sh or gaussian_sh_coefficients.shape[-1] == 1
+    dev = extrinsics.device
+    fov_x = torch.tensor(fov_degrees, device=dev).deg2rad()
+    tan_fov_x = (0.5 * fov_x).tan()
+    distance_to_near = (0.5 * width) / tan_fov_x
+    tan_fov_y = 0.5 * height / distance_to_near
+    fov_y = (2 * tan_fov_y).atan()  # sic (:166)
+    near = near + distance_to_near
+    far = far + distance_to_near
+    move_back = torch.eye(4, dtype=torch.float32, device=dev).repeat(b, 1, 1)
+    move_back[:, 2, 3] = -distance_to_near
+    extrinsics = extrinsics @ move_back
+    if dump is not None:
+        dump["extrinsics"] = extrinsics
+        dump["fov_x"] = fov_x
+        dump["fov_y"] = fov_y
+        dump["near"] = near
+        dump["far"] = far
+    projection_matrix = get_projection_matrix(near, far, fov_x.expand(b), fov_y).transpose(1, 2)
+    view_matrix = _inverse(extrinsics).transpose(1, 2)
+    full_projection = view_matrix @ projection_matrix
+    cams = pack_cameras_explicit(view_matrix, full_projection, extrinsics[:, :3, 3], tan_fov_x.expand(b), tan_fov_y,
+                                 background_color)
+    g = Gaussians(gaussian_means, gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities)
+    color, _, _ = render_views(g, extrinsics[:, None], None, near[:, None], far[:, None], image_shape,
+                               background_color, None, use_sh=use_sh, cams=cams)
+    return color.reshape(b, 3, *image_shape)
+
+
+def _contribution_stats(radii: Tensor, opacities: Tensor, opacity_threshold: float) -> list:
+    """cuda_splatting.py:353-369 for every (scene, view): radii [b,v,G], opacities [b,G]; one host read."""
+    b, v, G = radii.shape
+    visible = radii > 0
+    high = visible & (opacities >= opacity_threshold)[:, None, :]
+    counts = torch.stack((visible.sum(dim=-1), high.sum(dim=-1)), dim=-1).cpu()
+    stats = []
+    for i in range(b):
+        for j in range(v):
+            nv, nh = int(counts[i, j, 0]), int(counts[i, j, 1])
+            stats.append(GaussianContributionStats(
+                total_gaussians=G, visible_gaussians=nv, high_contribution_gaussians=nh,
+                visible_ratio=nv / G if G > 0 else 0.0, high_contribution_ratio=nh / G if G > 0 else 0.0,
+                opacity_threshold=opacity_threshold, radii=radii[i, j].clone()))
+    return stats
+
+
+def render_cuda_with_stats(extrinsics, intrinsics, near, far, image_shape, background_color, gaussian_means,
+                           gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities,
+                           scale_invariant: bool = True, use_sh: bool = True, opacity_threshold: float = 0.01):
+    """Signature of cuda_splatting.py:256-372: images [batch,3,h,w] + one GaussianContributionStats per batch
+    entry (visible = radii > 0; high contribution = visible and opacity >= threshold)."""
+    b = extrinsics.shape[0]
+    g = Gaussians(gaussian_means, gaussian_covariances, gaussian_sh_coefficients, gaussian_opacities)
+    color, _, radii = render_views(g, extrinsics[:, None], intrinsics[:, None], near[:, None], far[:, None],
+                                   image_shape, background_color, None, scale_invariant, want_radii=True,
+                                   use_sh=use_sh)
+    return color.reshape(b, 3, *image_shape), _contribution_stats(radii, gaussian_opacities, opacity_threshold)
 
 
 def render_depth_cuda(extrinsics, intrinsics, near, far, image_shape, gaussian_means, gaussian_covariances,
@@ -143,20 +212,7 @@ class DecoderSplattingCUDA(nn.Module):
         b, v = extrinsics.shape[:2]
         color, depth, radii = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
                                            self.background_color, depth_mode, want_radii=True)
-        stats = []
-        visible = radii > 0
-        high = visible & (gaussians.opacities >= opacity_threshold)[:, None, :]
-        n_visible = visible.sum(dim=-1).cpu()
-        n_high = high.sum(dim=-1).cpu()
-        G = radii.shape[-1]
-        for i in range(b):
-            for j in range(v):
-                nv, nh = int(n_visible[i, j]), int(n_high[i, j])
-                stats.append(GaussianContributionStats(
-                    total_gaussians=G, visible_gaussians=nv, high_contribution_gaussians=nh,
-                    visible_ratio=nv / G if G > 0 else 0.0, high_contribution_ratio=nh / G if G > 0 else 0.0,
-                    opacity_threshold=opacity_threshold, radii=radii[i, j].clone()))
-        return DecoderOutput(color, depth), stats
+        return DecoderOutput(color, depth), _contribution_stats(radii, gaussians.opacities, opacity_threshold)
 
 
 @dataclass
