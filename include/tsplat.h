@@ -120,6 +120,9 @@ typedef struct TsplatLayout {
   uint64_t status;        /* TsplatStatus                                                         */
   uint64_t depths;        /* float  [N, G]   camera-space z (the low key word)                    */
   uint64_t radii;         /* int32  [N, G]                                                        */
+  /* the next three are INTERLEAVED in one record of rec_stride (48) bytes per (view, Gaussian):
+   * x, y | conic.x, conic.y, conic.z, opacity | r, g, b, depth feature | id bits, cull threshold;
+   * element i of each section lives at section offset + i * rec_stride                            */
   uint64_t xy;            /* float2 [N, G]   pixel-space centre                                   */
   uint64_t conic_opacity; /* float4 [N, G]                                                        */
   uint64_t rgbd;          /* float4 [N, G]   r, g, b, depth feature                               */
@@ -135,6 +138,8 @@ typedef struct TsplatLayout {
   int32_t tiles_x, tiles_y; /* grid                                                               */
   int32_t sort_bits;      /* number of key bits the sort covers                                   */
   int32_t sort_passes;
+  int32_t rec_stride;     /* byte stride of the interleaved xy / conic_opacity / rgbd sections    */
+  int32_t reserved0;
 } TsplatLayout;
 
 /* Device-side status block (first bytes of the workspace). */

@@ -1,0 +1,45 @@
+"""torchrun --nproc-per-node N scripts/dist_gpu_check.py: view sharding over N GPUs (NCCL all-reduce of the flat
+per-Gaussian gradient slab, transplat_b200/parallel.py) against the same scene rendered whole on each rank."""
+import os, sys
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch
+import torch.distributed as dist
+from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+from transplat_b200.parallel import forward_view_sharded
+from transplat_b200.synthetic import make_scene, upstream_grads
+
+rank, local, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+V, HW = 8, 128
+sc = make_scene(n_ctx=2, h=64, w=64, n_views=V, render_hw=(HW, HW), seed=5)
+target, dLd = (t.to(dev) for t in upstream_grads(V, HW, HW, seed=9))
+dec = DecoderSplattingCUDA().to(dev)
+cam = [t[None].to(dev) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
+
+
+def leaves():
+    return [t[None].to(dev).requires_grad_(True) for t in (sc.means, sc.covariances, sc.harmonics, sc.opacities)]
+
+
+# whole scene on this rank
+L0 = leaves()
+out = dec.forward(Gaussians(*L0), *cam, (HW, HW), depth_mode="depth")
+loss = ((out.color[0] - target) ** 2).sum() + (out.depth[0] * dLd).sum()
+g_full = torch.autograd.grad(loss, L0)
+# view-sharded: this rank renders views rank, rank+world, ...
+L1 = leaves()
+out_s, mine = forward_view_sharded(dec, Gaussians(*L1), *cam, (HW, HW), depth_mode="depth")
+idx = torch.tensor(mine, device=dev)
+loss_s = ((out_s.color[0] - target[idx]) ** 2).sum() + (out_s.depth[0] * dLd[idx]).sum()
+g_shard = torch.autograd.grad(loss_s, L1)
+err = max(float((a - b).abs().max() / a.abs().max()) for a, b in zip(g_full, g_shard))
+img_err = float((out_s.color[0] - out.color[0, idx]).abs().max())
+t = torch.tensor([err, img_err], device=dev)
+dist.all_reduce(t, op=dist.ReduceOp.MAX)
+if rank == 0:
+    print(f"view sharding over {world} GPUs: views/rank {len(mine)}, max rel gradient error vs whole-scene {t[0]:.3e}, "
+          f"image error {t[1]:.3e}", "OK" if t[0] < 1e-4 and t[1] < 1e-5 else "FAIL")
+dist.destroy_process_group()

@@ -31,7 +31,8 @@ def step(s):
 for i in range(10):
     step(S[i % 2])
 torch.cuda.synchronize()
-_lib.profile_enable(True)
+PROF = os.environ.get('PROFILE', '1') == '1'
+_lib.profile_enable(PROF)
 n = int(os.environ.get("STEPS", 40))
 ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
 for i in range(n):
@@ -40,7 +41,7 @@ for i in range(n):
     step(S[i % 2])
     ev[i][1].record()
 torch.cuda.synchronize()
-st = _lib.profile_read()
+st = _lib.profile_read() if PROF else {}
 ms = sorted(a.elapsed_time(b) for a, b in ev)
 print(os.environ.get("TAG", "?"), "step_ms median %.4f mean %.4f |" % (ms[n // 2], sum(ms) / n),
       " ".join(f"{k}={v:.4f}" for k, v in st.items() if k != "calls" and v > 0))

@@ -42,7 +42,10 @@ def test_workspace_layout_c2():
     assert (lay.tiles_x, lay.tiles_y) == (16, 16)
     assert lay.sort_bits == 32 + 10 and lay.sort_passes == 6   # 4 views x 256 tiles = 2^10 (view, tile) ids
     offs = [getattr(lay, n) for n, _ in _lib.TsplatLayout._fields_[1:15]]
-    assert all(o % 256 == 0 for o in offs) and len(set(offs)) == len(offs)
+    # xy / conic_opacity / rgbd are interleaved in one 48-byte record per (view, Gaussian)
+    assert lay.rec_stride == 48 and lay.conic_opacity == lay.xy + 8 and lay.rgbd == lay.xy + 24
+    aligned = [o for o in offs if o not in (lay.conic_opacity, lay.rgbd)]
+    assert all(o % 256 == 0 for o in aligned) and len(set(offs)) == len(offs)
     assert lay.status == 0 and max(offs) < lay.total_bytes
 
 

@@ -34,6 +34,30 @@ def _worker(rank, world, port, ret):
           torch.allclose(g.covariances.grad, torch.full_like(g.covariances, 2.0 * tot)) and
           torch.allclose(g.harmonics.grad, torch.full_like(g.harmonics, 3.0 * tot)) and
           torch.allclose(g.opacities.grad, torch.full_like(g.opacities, 4.0 * tot)))
+    # gradients that arrive as views of ONE flat slab (what the rasterizer's backward returns) take the in-place path
+    class _SlabGrads(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, m, c, h, o):
+            ctx.shapes = [t.shape for t in (m, c, h, o)]
+            return m.sum() + c.sum() + h.sum() + o.sum()
+
+        @staticmethod
+        def backward(ctx, gout):
+            sizes = [int(torch.Size(s).numel()) for s in ctx.shapes]
+            slab = torch.empty(sum(sizes) + 64 * 3)
+            outs, off = [], 0
+            for k, (n, shp) in enumerate(zip(sizes, ctx.shapes)):
+                v = slab[off:off + n].view(shp)
+                v.fill_(float(k + 1) * (rank + 1))
+                outs.append(v)
+                off += n + 64
+            return tuple(outs)
+
+    g2 = Gaussians(*(t.detach().clone().requires_grad_(True) for t in (g.means, g.covariances, g.harmonics, g.opacities)))
+    r2 = replicate_with_summed_grads(g2)
+    _SlabGrads.apply(r2.means, r2.covariances, r2.harmonics, r2.opacities).backward()
+    for k, t in enumerate((g2.means, g2.covariances, g2.harmonics, g2.opacities)):
+        ok = ok and torch.allclose(t.grad, torch.full_like(t, float(k + 1) * tot))
     ret[rank] = bool(ok)
     dist.destroy_process_group()
 

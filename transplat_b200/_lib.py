@@ -33,7 +33,7 @@ class TsplatLayout(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "total_bytes", "status", "depths", "radii", "xy", "conic_opacity", "rgbd", "tiles_touched",
         "clamped", "keys", "vals", "ranges", "final_T", "n_contrib", "grad_acc")] + [
-        (n, C.c_int32) for n in ("tiles_x", "tiles_y", "sort_bits", "sort_passes")]
+        (n, C.c_int32) for n in ("tiles_x", "tiles_y", "sort_bits", "sort_passes", "rec_stride", "reserved0")]
 
 
 class TsplatStatus(C.Structure):

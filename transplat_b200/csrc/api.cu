@@ -79,9 +79,10 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   // ---- per (view, Gaussian) state ----
   L.depths = take(4 * NG);
   L.radii = take(4 * NG);
-  L.xy = take(8 * NG);
-  L.conic_opacity = take(16 * NG);
-  L.rgbd = take(16 * NG);
+  // one 48-B record per (view, Gaussian): x, y, conic.xyz, opacity, r, g, b, depth feature, id bits, cull threshold
+  const uint64_t grec = take(48 * NG);
+  L.xy = grec; L.conic_opacity = grec + 8; L.rgbd = grec + 24;
+  L.rec_stride = 48; L.reserved0 = 0;
   L.tiles_touched = take(4 * NG);
   L.clamped = take(NG);
   // ---- pair list (double-buffered for the radix passes) ----
@@ -109,9 +110,7 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   w.ctl = reinterpret_cast<Control*>(b + L.status);
   w.depths = reinterpret_cast<float*>(b + L.depths);
   w.radii = reinterpret_cast<int*>(b + L.radii);
-  w.xy = reinterpret_cast<float2*>(b + L.xy);
-  w.conic_opacity = reinterpret_cast<float4*>(b + L.conic_opacity);
-  w.rgbd = reinterpret_cast<float4*>(b + L.rgbd);
+  w.grec = reinterpret_cast<float4*>(b + L.xy);
   w.tiles_touched = reinterpret_cast<unsigned int*>(b + L.tiles_touched);
   w.clamped = reinterpret_cast<unsigned char*>(b + L.clamped);
   const bool odd = L.sort_passes & 1;  // buffer 0 is where bin_emit writes; sorted result lands in [passes & 1]

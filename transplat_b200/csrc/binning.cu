@@ -69,7 +69,7 @@ __global__ void __launch_bounds__(kScanThreads) bin_emit_kernel(Workspace ws, in
     run += cnt[i];
     const int it = item0 + i;
     if (cnt[i] != 0) {
-      const float2 c = ws.xy[it];
+      const float2 c = *reinterpret_cast<const float2*>(ws.grec + it * 3);
       int x0, y0, x1, y1;
       get_rect(c.x, c.y, ws.radii[it], ws.tiles_x, ws.tiles_y, x0, y0, x1, y1);
       s_rect[li] = (unsigned)x0 | ((unsigned)y0 << 10) | ((unsigned)(x1 - x0) << 20);
@@ -344,12 +344,10 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
     if (j == D - 1) ws.ranges[tile].y = D;
     const unsigned int id = vals[j];
     const size_t o = (size_t)(tile / (unsigned)ws.T) * G + id;
-    const float2 c = ws.xy[o];
-    const float4 co = ws.conic_opacity[o];
-    const float4 f = ws.rgbd[o];
-    ws.rec0[j] = make_float4(c.x, c.y, co.x, co.y);
-    ws.rec1[j] = make_float4(co.z, co.w, f.x, f.y);
-    ws.rec2[j] = make_float4(f.z, f.w, __uint_as_float(id), cull_tau(co.x, co.y, co.z, co.w));
+    const float4* __restrict__ gr = ws.grec + o * 3;
+    ws.rec0[j] = gr[0];
+    ws.rec1[j] = gr[1];
+    ws.rec2[j] = gr[2];
   }
   if (!ws.use_order) return;
   // The last CTA to finish orders the (view, tile) ids by list length, longest first (counting sort

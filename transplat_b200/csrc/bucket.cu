@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(256) bucket_emit_kernel(Workspace ws, int G, u
   int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
   unsigned long long word = 0;
   if (live) {
-    const float2 c = ws.xy[it];
+    const float2 c = *reinterpret_cast<const float2*>(ws.grec + it * 3);
     get_rect(c.x, c.y, ws.radii[it], ws.tiles_x, ws.tiles_y, x0, y0, x1, y1);
     word = ((unsigned long long)__float_as_uint(ws.depths[it]) << 32) | (unsigned int)g;
   }
@@ -228,42 +228,43 @@ __device__ __forceinline__ void bitonic_sort_words(unsigned long long* s, int n,
   }
 }
 
-// write keys / values / records of one sorted tile segment
+// write keys / values of one sorted tile segment (the records follow in gather_records_kernel)
 __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const unsigned long long* s, int n, unsigned int start,
                                                   int bid, int G, unsigned long long* __restrict__ keys_out,
                                                   unsigned int* __restrict__ vals_out, int tid, int nthreads) {
-  const size_t vbase = (size_t)(bid / ws.T) * G;
   const unsigned long long hiw = (unsigned long long)(unsigned int)bid << 32;
-  constexpr int U = 4;  // entries in flight per thread: the gathers are L2-latency bound
-  for (int j0 = tid; j0 < n; j0 += U * nthreads) {
-    unsigned long long w[U];
-    float2 c[U];
-    float4 co[U], f[U];
+  for (int j = tid; j < n; j += nthreads) {
+    const unsigned long long w = s[j];
+    keys_out[start + j] = hiw | (w >> 32);
+    vals_out[start + j] = (unsigned int)w;
+  }
+}
+
+// 5. gather of the 48-B per-Gaussian records (preprocess.cu) into sorted order: one thread per pair over the whole
+//    sorted list, full occupancy, coalesced 16-B stores to rec0/rec1/rec2 - what the render kernels stream with TMA.
+//    (Inside the per-tile sort CTAs - 2 per SM, load/sort/write phases serialised - the same copy took twice as long.)
+__global__ void __launch_bounds__(256) gather_records_kernel(Workspace ws, int G,
+                                                             const unsigned long long* __restrict__ keys,
+                                                             const unsigned int* __restrict__ vals) {
+  const unsigned long long Dfull = ws.ctl->num_rendered;
+  const unsigned int D = (unsigned int)(Dfull < ws.d_cap ? Dfull : ws.d_cap);
+  constexpr int U = 2;
+  const unsigned int stride = gridDim.x * blockDim.x;
+  for (unsigned int j0 = blockIdx.x * blockDim.x + threadIdx.x; j0 < D; j0 += U * stride) {
+    float4 q[U][3];
 #pragma unroll
     for (int u = 0; u < U; u++) {
-      const int j = j0 + u * nthreads;
-      w[u] = j < n ? s[j] : 0ull;
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const int j = j0 + u * nthreads;
-      if (j < n) {
-        const size_t o = vbase + (unsigned int)w[u];
-        c[u] = ws.xy[o]; co[u] = ws.conic_opacity[o]; f[u] = ws.rgbd[o];
+      const unsigned int j = j0 + u * stride;
+      if (j < D) {
+        const unsigned int bid = (unsigned int)(keys[j] >> 32);
+        const float4* __restrict__ gr = ws.grec + ((size_t)(bid / (unsigned)ws.T) * G + vals[j]) * 3;
+        q[u][0] = gr[0]; q[u][1] = gr[1]; q[u][2] = gr[2];
       }
     }
 #pragma unroll
     for (int u = 0; u < U; u++) {
-      const int j = j0 + u * nthreads;
-      if (j < n) {
-        const unsigned int id = (unsigned int)w[u];
-        keys_out[start + j] = hiw | (w[u] >> 32);
-        vals_out[start + j] = id;
-        ws.rec0[start + j] = make_float4(c[u].x, c[u].y, co[u].x, co[u].y);
-        ws.rec1[start + j] = make_float4(co[u].z, co[u].w, f[u].x, f[u].y);
-        ws.rec2[start + j] = make_float4(f[u].z, f[u].w, __uint_as_float(id),
-                                         cull_tau(co[u].x, co[u].y, co[u].z, co[u].w));
-      }
+      const unsigned int j = j0 + u * stride;
+      if (j < D) { ws.rec0[j] = q[u][0]; ws.rec1[j] = q[u][1]; ws.rec2[j] = q[u][2]; }
     }
   }
 }
@@ -275,13 +276,99 @@ __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const uns
 constexpr int kTileSortThreads = 512;
 constexpr int kTileSortWarps = kTileSortThreads / 32;
 
+constexpr int kDepthBuckets = 4096;  // depth buckets of the distribution sort (>= kSmallTileCap keeps ~1 word/bucket)
+constexpr int kMaxBucketFill = 48;   // a fuller bucket (clustered or equal depths) sends the tile to the radix path
+
 struct TileSortSmem {
   unsigned long long words[kSmallTileCap];
-  unsigned int whist[kTileSortWarps][kRadix];  // per-warp digit counts -> exclusive prefixes over warps
+  union {
+    unsigned long long tmp[kSmallTileCap];       // distribution sort: words grouped by bucket
+    unsigned int whist[kTileSortWarps][kRadix];  // radix path: per-warp digit counts -> exclusive prefixes over warps
+  };
+  unsigned int bucket[kDepthBuckets + 1];        // counts -> exclusive bases (bucket[kDepthBuckets] = n)
   unsigned int dexcl[kRadix];                  // exclusive offset of each digit in the CTA
-  unsigned int wscan[8];
+  unsigned int wscan[kTileSortWarps];
   unsigned int nruns;
+  unsigned int dmin, dmax, maxfill;
 };
+
+// Distribution sort of the tile's words (depth bits << 32 | Gaussian id, all distinct) - the default.  The depth
+// range of the tile is cut into kDepthBuckets equal intervals of the BIT PATTERN (monotone for positive floats):
+//   count per bucket (shared-memory atomics) -> exclusive scan -> scatter by bucket -> every word finds its rank
+//   among the (typically 1-3) words of its bucket by comparing whole words.
+// The result is the ascending order of the words, i.e. the stable depth sort of the Gaussian-ordered list, with
+// one pass over the data instead of the radix sort's four.  Returns false (nothing modified) when some bucket
+// holds more than kMaxBucketFill words; the caller then takes the radix path.
+__device__ __forceinline__ bool distribution_sort_tile(TileSortSmem& s, int n, int tid) {
+  const int lane = tid & 31, warp = tid >> 5;
+  constexpr int KMAX = kSmallTileCap / kTileSortThreads;  // 8 words per thread at most
+  for (int i = tid; i <= kDepthBuckets; i += kTileSortThreads) s.bucket[i] = 0u;
+  unsigned int lo = 0xffffffffu, hi = 0u;
+  for (int i = tid; i < n; i += kTileSortThreads) {
+    const unsigned int d = (unsigned int)(s.words[i] >> 32);
+    lo = min(lo, d); hi = max(hi, d);
+  }
+  lo = __reduce_min_sync(0xffffffffu, lo);
+  hi = __reduce_max_sync(0xffffffffu, hi);
+  if (lane == 0) { atomicMin(&s.dmin, lo); atomicMax(&s.dmax, hi); }
+  __syncthreads();
+  const unsigned int dmin = s.dmin, range = s.dmax - dmin;
+  const int bits = 32 - __clz(range);  // 0 when every depth is equal
+  const int shift = max(0, bits - 12);
+  unsigned short rank[KMAX];
+#pragma unroll
+  for (int k = 0; k < KMAX; k++) {
+    const int i = tid + k * kTileSortThreads;
+    if (i < n) {
+      const unsigned int b = ((unsigned int)(s.words[i] >> 32) - dmin) >> shift;
+      rank[k] = (unsigned short)atomicAdd(&s.bucket[b], 1u);
+    }
+  }
+  __syncthreads();
+  {  // exclusive scan of the counts: thread t owns buckets [8t, 8t+8)
+    constexpr int PER = kDepthBuckets / kTileSortThreads;
+    unsigned int c[PER], sum = 0, mx = 0;
+#pragma unroll
+    for (int k = 0; k < PER; k++) { c[k] = s.bucket[tid * PER + k]; sum += c[k]; mx = max(mx, c[k]); }
+    unsigned int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    mx = __reduce_max_sync(0xffffffffu, mx);
+    if (lane == 31) s.wscan[warp] = incl;
+    if (lane == 0) atomicMax(&s.maxfill, mx);
+    __syncthreads();
+    unsigned int pre = incl - sum;
+    for (int wv = 0; wv < warp; wv++) pre += s.wscan[wv];
+#pragma unroll
+    for (int k = 0; k < PER; k++) { s.bucket[tid * PER + k] = pre; pre += c[k]; }
+    if (tid == 0) s.bucket[kDepthBuckets] = (unsigned int)n;
+  }
+  __syncthreads();
+  if (s.maxfill > (unsigned int)kMaxBucketFill) return false;
+#pragma unroll
+  for (int k = 0; k < KMAX; k++) {
+    const int i = tid + k * kTileSortThreads;
+    if (i < n) {
+      const unsigned long long w = s.words[i];
+      const unsigned int b = ((unsigned int)(w >> 32) - dmin) >> shift;
+      s.tmp[s.bucket[b] + rank[k]] = w;
+    }
+  }
+  __syncthreads();
+  for (int i = tid; i < n; i += kTileSortThreads) {
+    const unsigned long long w = s.tmp[i];
+    const unsigned int b = ((unsigned int)(w >> 32) - dmin) >> shift;
+    const unsigned int b0 = s.bucket[b], b1 = s.bucket[b + 1];
+    unsigned int r = 0;
+    for (unsigned int q = b0; q < b1; q++) r += s.tmp[q] < w ? 1u : 0u;
+    s.words[b0 + r] = w;
+  }
+  __syncthreads();
+  return true;
+}
 
 template <int KPT>
 __device__ __forceinline__ void radix_sort_tile_by_depth(TileSortSmem& s, int n, int tid) {
@@ -369,33 +456,42 @@ __global__ void __launch_bounds__(kTileSortThreads, 2) tile_sort_gather_kernel(W
   if (n == 0 || n > kSmallTileCap) return;
   const int tid = threadIdx.x;
   for (int i = tid; i < n; i += kTileSortThreads) s.words[i] = pairs[r.x + i];
-  if (tid == 0) s.nruns = 0;
+  if (tid == 0) { s.nruns = 0; s.dmin = 0xffffffffu; s.dmax = 0u; s.maxfill = 0u; }
   __syncthreads();
-  if (n <= 1 * kTileSortThreads) radix_sort_tile_by_depth<1>(s, n, tid);
-  else if (n <= 2 * kTileSortThreads) radix_sort_tile_by_depth<2>(s, n, tid);
-  else if (n <= 4 * kTileSortThreads) radix_sort_tile_by_depth<4>(s, n, tid);
-  else radix_sort_tile_by_depth<8>(s, n, tid);
-  // equal depths: the words of a run are still in emission (atomic) order; order them by Gaussian id
-  unsigned int* runs = &s.whist[0][0];  // free now: up to kTileSortWarps*kRadix = 4096 run starts
-  for (int i = tid; i + 1 < n; i += kTileSortThreads) {
-    const unsigned int d = (unsigned int)(s.words[i] >> 32);
-    if ((unsigned int)(s.words[i + 1] >> 32) == d && (i == 0 || (unsigned int)(s.words[i - 1] >> 32) != d))
-      runs[atomicAdd(&s.nruns, 1u)] = (unsigned int)i;
-  }
-  __syncthreads();
-  for (unsigned int k = tid; k < s.nruns; k += kTileSortThreads) {
-    const int b0 = (int)runs[k];
-    const unsigned int d = (unsigned int)(s.words[b0] >> 32);
-    int e = b0 + 1;
-    while (e < n && (unsigned int)(s.words[e] >> 32) == d) e++;
-    for (int i = b0 + 1; i < e; i++) {  // insertion sort of the run (whole words: same high half)
-      const unsigned long long x = s.words[i];
-      int j = i - 1;
-      while (j >= b0 && s.words[j] > x) { s.words[j + 1] = s.words[j]; j--; }
-      s.words[j + 1] = x;
+#if defined(TSPLAT_EXP_RADIX_ONLY)
+  const bool sorted = false;
+#elif defined(TSPLAT_EXP_NOSORT)
+  const bool sorted = true;
+#else
+  const bool sorted = distribution_sort_tile(s, n, tid);
+#endif
+  if (!sorted) {  // clustered / equal depths: 4-pass LSD radix sort on the depth half + fix-up of equal-depth runs
+    if (n <= 1 * kTileSortThreads) radix_sort_tile_by_depth<1>(s, n, tid);
+    else if (n <= 2 * kTileSortThreads) radix_sort_tile_by_depth<2>(s, n, tid);
+    else if (n <= 4 * kTileSortThreads) radix_sort_tile_by_depth<4>(s, n, tid);
+    else radix_sort_tile_by_depth<8>(s, n, tid);
+    // equal depths: the words of a run are still in emission (atomic) order; order them by Gaussian id
+    unsigned int* runs = &s.whist[0][0];  // free now: up to kTileSortWarps*kRadix = 4096 run starts
+    for (int i = tid; i + 1 < n; i += kTileSortThreads) {
+      const unsigned int d = (unsigned int)(s.words[i] >> 32);
+      if ((unsigned int)(s.words[i + 1] >> 32) == d && (i == 0 || (unsigned int)(s.words[i - 1] >> 32) != d))
+        runs[atomicAdd(&s.nruns, 1u)] = (unsigned int)i;
     }
+    __syncthreads();
+    for (unsigned int k = tid; k < s.nruns; k += kTileSortThreads) {
+      const int b0 = (int)runs[k];
+      const unsigned int d = (unsigned int)(s.words[b0] >> 32);
+      int e = b0 + 1;
+      while (e < n && (unsigned int)(s.words[e] >> 32) == d) e++;
+      for (int i = b0 + 1; i < e; i++) {  // insertion sort of the run (whole words: same high half)
+        const unsigned long long x = s.words[i];
+        int j = i - 1;
+        while (j >= b0 && s.words[j] > x) { s.words[j + 1] = s.words[j]; j--; }
+        s.words[j + 1] = x;
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
   write_sorted_tile(ws, s.words, n, r.x, bid, G, keys_out, vals_out, tid, kTileSortThreads);
 }
 
@@ -454,6 +550,9 @@ cudaError_t launch_bucket_sort_gather(const TsplatProblem& p, const Workspace& w
   e = cudaFuncSetAttribute(big_tile_sort_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   if (e != cudaSuccess) return e;
   big_tile_sort_gather_kernel<<<148, 512, smem, st>>>(ws, p.G, pairs, keys_out, vals_out);
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  gather_records_kernel<<<148 * 8, 256, 0, st>>>(ws, p.G, keys_out, vals_out);
   return cudaGetLastError();
 }
 

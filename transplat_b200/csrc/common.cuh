@@ -14,7 +14,14 @@ namespace tsplat {
 
 constexpr int kTile = TSPLAT_TILE;          // 16x16 pixels per tile (parity contract)
 constexpr int kTilePix = kTile * kTile;     // 256
-constexpr int kPreBlock = 128;              // Gaussians per preprocess CTA
+#ifndef TSPLAT_PRE_BLOCK
+#define TSPLAT_PRE_BLOCK 128
+#endif
+constexpr int kPreBlock = TSPLAT_PRE_BLOCK;
+#ifndef TSPLAT_PRE_BLOCK_BWD
+#define TSPLAT_PRE_BLOCK_BWD 64
+#endif
+constexpr int kPreBwdBlock = TSPLAT_PRE_BLOCK_BWD;  // Gaussians per preprocess-backward CTA              // Gaussians per preprocess CTA
 constexpr int kScanThreads = 256;
 constexpr int kScanItems = 4;               // (view, Gaussian) items per thread in bin_emit
 constexpr int kScanTile = kScanThreads * kScanItems;
@@ -48,9 +55,8 @@ struct Workspace {
   Control* ctl;
   float* depths;
   int* radii;
-  float2* xy;
-  float4* conic_opacity;
-  float4* rgbd;
+  float4* grec;  // per (view, Gaussian) record, 3 x float4 in the layout of rec0/rec1/rec2 below: the gather into
+                 // sorted order is a plain 48-B copy, and the cull threshold is computed once per Gaussian
   unsigned int* tiles_touched;
   unsigned char* clamped;
   unsigned long long* keys[2];
@@ -61,7 +67,7 @@ struct Workspace {
   float* grad_acc;
   float4* rec0;  // x, y, conic.x, conic.y                      (sorted order)
   float4* rec1;  // conic.z, opacity, r, g
-  float4* rec2;  // b, depth feature, bits(Gaussian id), 0
+  float4* rec2;  // b, depth feature, bits(Gaussian id), cull threshold tau_s (cull.cuh)
   unsigned int* tile_count;        // bucket path: pairs per (view, tile), counted by the preprocess kernel
   unsigned int* tile_cursor;       // bucket path: emission cursors per (view, tile)
   unsigned int* big_list;          // bucket path: (view, tile) ids with more than kSmallTileCap pairs

@@ -10,6 +10,7 @@
 // from HBM once per scene instead of once per view (the reference re-reads and re-copies it per
 // view: decoder_splatting_cuda.py:59-62, cuda_splatting.py:84).  HBM-bound: 340 B read once +
 // 53 B written per (view, Gaussian).
+#include "cull.cuh"
 #include "geom.cuh"
 
 namespace tsplat {
@@ -179,9 +180,14 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a
     }
     ws.depths[o] = depth;
     ws.radii[o] = radius;
-    ws.xy[o] = make_float2(px, py);
-    ws.conic_opacity[o] = con_o;
-    ws.rgbd[o] = rgbd;
+    {
+      // the record the binning stage copies into sorted order (render.cu reads it as rec0/rec1/rec2)
+      float4* gr = ws.grec + o * 3;
+      const float tau = radius > 0 ? cull_tau(con_o.x, con_o.y, con_o.z, con_o.w) : 0.0f;
+      gr[0] = make_float4(px, py, con_o.x, con_o.y);
+      gr[1] = make_float4(con_o.z, con_o.w, rgbd.x, rgbd.y);
+      gr[2] = make_float4(rgbd.z, rgbd.w, __uint_as_float((unsigned int)g), tau);
+    }
     ws.tiles_touched[o] = touched;
     ws.clamped[o] = cl;
     if (out_radii) out_radii[o] = radius;

@@ -21,40 +21,40 @@ struct PreBwdArgs {
   float* dL_dmeans2D;
 };
 
-__global__ void __launch_bounds__(kPreBlock) preprocess_backward_kernel(PreBwdArgs a, Workspace ws) {
+__global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBwdArgs a, Workspace ws) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
   float* s_mean = reinterpret_cast<float*>(smem_raw + 16);
-  float* s_cov = s_mean + 3 * kPreBlock;
-  float* s_sh = s_cov + a.cov_floats * kPreBlock;
-  float* s_dsh = s_sh + a.sh_floats * kPreBlock;
+  float* s_cov = s_mean + 3 * kPreBwdBlock;
+  float* s_sh = s_cov + a.cov_floats * kPreBwdBlock;
+  float* s_dsh = s_sh + a.sh_floats * kPreBwdBlock;
 
   const TsplatProblem& p = a.p;
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
-  const int g0 = blockIdx.x * kPreBlock;
-  const int cnt = min(kPreBlock, p.G - g0);
+  const int g0 = blockIdx.x * kPreBwdBlock;
+  const int cnt = min(kPreBwdBlock, p.G - g0);
   const size_t gbase = (size_t)b * p.G + g0;
   const float* g_mean = p.means + gbase * 3;
   const float* g_cov = p.cov + gbase * a.cov_floats;
   const float* g_sh = p.sh + gbase * a.sh_floats;
 
-  const bool bulk = a.bulk_ok && cnt == kPreBlock;
+  const bool bulk = a.bulk_ok && cnt == kPreBwdBlock;
   if (bulk) {
     if (tid == 0) {
       mbar_init(bar, 1);
       mbar_fence_init();
-      mbar_expect_tx(bar, (uint32_t)(kPreBlock * (12 + 4 * a.cov_floats + 4 * a.sh_floats)));
-      bulk_g2s(s_mean, g_mean, kPreBlock * 12, bar);
-      bulk_g2s(s_cov, g_cov, kPreBlock * 4 * a.cov_floats, bar);
-      bulk_g2s(s_sh, g_sh, kPreBlock * 4 * a.sh_floats, bar);
+      mbar_expect_tx(bar, (uint32_t)(kPreBwdBlock * (12 + 4 * a.cov_floats + 4 * a.sh_floats)));
+      bulk_g2s(s_mean, g_mean, kPreBwdBlock * 12, bar);
+      bulk_g2s(s_cov, g_cov, kPreBwdBlock * 4 * a.cov_floats, bar);
+      bulk_g2s(s_sh, g_sh, kPreBwdBlock * 4 * a.sh_floats, bar);
     }
   } else {
-    for (int i = tid; i < cnt * 3; i += kPreBlock) s_mean[i] = g_mean[i];
-    for (int i = tid; i < cnt * a.cov_floats; i += kPreBlock) s_cov[i] = g_cov[i];
-    for (int i = tid; i < cnt * a.sh_floats; i += kPreBlock) s_sh[i] = g_sh[i];
+    for (int i = tid; i < cnt * 3; i += kPreBwdBlock) s_mean[i] = g_mean[i];
+    for (int i = tid; i < cnt * a.cov_floats; i += kPreBwdBlock) s_cov[i] = g_cov[i];
+    for (int i = tid; i < cnt * a.sh_floats; i += kPreBwdBlock) s_sh[i] = g_sh[i];
   }
-  for (int i = tid; i < kPreBlock * a.sh_floats; i += kPreBlock) s_dsh[i] = 0.0f;
+  for (int i = tid; i < kPreBwdBlock * a.sh_floats; i += kPreBwdBlock) s_dsh[i] = 0.0f;
   __syncthreads();
   if (bulk) mbar_wait(bar, 0);
 
@@ -74,24 +74,41 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_backward_kernel(PreBwdAr
     const float* my_sh = s_sh + (size_t)tid * a.sh_floats;
     float* my_dsh = s_dsh + (size_t)tid * a.sh_floats;
 
+    // per-view inputs are fetched one view AHEAD: the loop body is ~1500 dependent instructions per view and only
+    // 8 warps fit on an SM (648 B of shared memory per Gaussian), so nothing else hides the L2/HBM latency
+    struct ViewIn { float4 q0, q1, q2; int radius; unsigned char cl; };
+    auto fetch = [&](int v) {
+      ViewIn in;
+      const size_t o = (size_t)(b * p.V + v) * p.G + g;
+      in.radius = ws.radii[o];
+      in.cl = ws.clamped[o];
+      const float4* ga = reinterpret_cast<const float4*>(ws.grad_acc + o * kAccFloats);
+      const float4 z = make_float4(0.f, 0.f, 0.f, 0.f);
+      in.q0 = in.radius > 0 ? ga[0] : z;  // accumulators of culled Gaussians are never initialised
+      in.q1 = in.radius > 0 ? ga[1] : z;
+      in.q2 = in.radius > 0 ? ga[2] : z;
+      return in;
+    };
+    ViewIn nxt = fetch(0);
     for (int v = 0; v < p.V; v++) {
       const int n = b * p.V + v;
       const size_t o = (size_t)n * p.G + g;
-      const bool vis = ws.radii[o] > 0;
+      const ViewIn cur = nxt;
+      if (v + 1 < p.V) nxt = fetch(v + 1);
+      const bool vis = cur.radius > 0;
       if (a.dL_dmeans2D) {
         float* d2 = a.dL_dmeans2D + o * 3;
-        d2[0] = vis ? ws.grad_acc[o * kAccFloats + 0] : 0.0f;
-        d2[1] = vis ? ws.grad_acc[o * kAccFloats + 1] : 0.0f;
+        d2[0] = vis ? cur.q0.x : 0.0f;
+        d2[1] = vis ? cur.q0.y : 0.0f;
         d2[2] = 0.0f;
       }
       if (!vis) continue;
-      const float4* ga = reinterpret_cast<const float4*>(ws.grad_acc + o * kAccFloats);
-      const float4 q0 = ga[0], q1 = ga[1], q2 = ga[2];
+      const float4 q0 = cur.q0, q1 = cur.q1, q2 = cur.q2;
       const float dmx = q0.x, dmy = q0.y;
       const float dcon[3] = {q0.z, q0.w, q1.x};
       gop += q1.y;
       float dcol[4] = {q1.z, q1.w, q2.x, q2.y};
-      const unsigned char cl = ws.clamped[o];
+      const unsigned char cl = cur.cl;
 
       const float* cam = reinterpret_cast<const float*>(p.cams + n);
       const float* vm = cam;
@@ -105,6 +122,9 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_backward_kernel(PreBwdAr
       const float fx = (float)p.W / (2.0f * tanx), fy = (float)p.H / (2.0f * tany);
 
       // ---- cov2D backward (A.4) ----
+#ifdef TSPLAT_EXP_NOCOV
+      if (dmx == 123.456f) continue;
+#endif
       Cov2D q;
       compute_cov2d(m, fx, fy, tanx, tany, c6, vm, q);
       const float aa = q.a, bb = q.b, cc = q.c;
@@ -156,7 +176,11 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_backward_kernel(PreBwdAr
       dmean[2] += (pj[8] * m_w - pj[11] * mul1) * dmx + (pj[9] * m_w - pj[11] * mul2) * dmy;
 
       // ---- SH backward (A.5) ----
+#ifdef TSPLAT_EXP_NOSH
+      if (M > 0 && dcol[0] == 123.456f) {
+#else
       if (M > 0) {
+#endif
 #pragma unroll
         for (int ch = 0; ch < 3; ch++)
           if (cl & (1u << ch)) dcol[ch] = 0.0f;
@@ -220,12 +244,12 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_backward_kernel(PreBwdAr
     fence_proxy_async();
     __syncthreads();
     if (tid == 0) {
-      bulk_s2g(g_dsh, s_dsh, (uint32_t)(kPreBlock * 4 * a.sh_floats));
+      bulk_s2g(g_dsh, s_dsh, (uint32_t)(kPreBwdBlock * 4 * a.sh_floats));
       bulk_commit();
       bulk_wait_all();
     }
   } else {
-    for (int i = tid; i < cnt * a.sh_floats; i += kPreBlock) g_dsh[i] = s_dsh[i];
+    for (int i = tid; i < cnt * a.sh_floats; i += kPreBwdBlock) g_dsh[i] = s_dsh[i];
   }
 }
 
@@ -240,12 +264,12 @@ cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& 
   a.bulk_ok = al16(p.means) && al16(p.cov) && al16(p.sh) && al16(dL_dsh) && stride_ok;
   a.dL_dmeans = dL_dmeans; a.dL_dcov = dL_dcov; a.dL_dsh = dL_dsh; a.dL_dopacity = dL_dopacity;
   a.dL_dmeans2D = dL_dmeans2D;
-  const size_t smem = 16 + sizeof(float) * kPreBlock * (3 + a.cov_floats + 2 * a.sh_floats);
+  const size_t smem = 16 + sizeof(float) * kPreBwdBlock * (3 + a.cov_floats + 2 * a.sh_floats);
   cudaError_t e = cudaFuncSetAttribute(preprocess_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem);
   if (e != cudaSuccess) return e;
-  dim3 grid((p.G + kPreBlock - 1) / kPreBlock, p.B);
-  preprocess_backward_kernel<<<grid, kPreBlock, smem, st>>>(a, ws);
+  dim3 grid((p.G + kPreBwdBlock - 1) / kPreBwdBlock, p.B);
+  preprocess_backward_kernel<<<grid, kPreBwdBlock, smem, st>>>(a, ws);
   return cudaGetLastError();
 }
 

@@ -331,9 +331,10 @@ def inspect_workspace(state) -> dict:
         "sort_bits": lay.sort_bits,
         "depths": sec(lay.depths, 4 * N * G, torch.float32, (N, G)),
         "radii": sec(lay.radii, 4 * N * G, torch.int32, (N, G)),
-        "xy": sec(lay.xy, 8 * N * G, torch.float32, (N, G, 2)),
-        "conic_opacity": sec(lay.conic_opacity, 16 * N * G, torch.float32, (N, G, 4)),
-        "rgbd": sec(lay.rgbd, 16 * N * G, torch.float32, (N, G, 4)),
+        # interleaved 48-B records: x, y | conic.xyz, opacity | r, g, b, depth feature | id, cull threshold
+        "xy": sec(lay.xy, lay.rec_stride * N * G, torch.float32, (N, G, lay.rec_stride // 4))[..., 0:2],
+        "conic_opacity": sec(lay.xy, lay.rec_stride * N * G, torch.float32, (N, G, lay.rec_stride // 4))[..., 2:6],
+        "rgbd": sec(lay.xy, lay.rec_stride * N * G, torch.float32, (N, G, lay.rec_stride // 4))[..., 6:10],
         "tiles_touched": sec(lay.tiles_touched, 4 * N * G, torch.int32, (N, G)),
         "clamped": sec(lay.clamped, N * G, torch.uint8, (N, G)),
         "keys": sec(lay.keys, 8 * D, torch.int64, (D,)),
