@@ -209,6 +209,45 @@ int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* c
 int tsplat_profile_enable(int on);
 int tsplat_profile_read(float* ms_host, int n);
 
+/* ------------------------------------------------------------------------------------------------------------
+ * The step BEFORE the render path: the per-pixel Gaussian producer.  Replaces the torch op chain of
+ *   GaussianAdapter.forward           src/model/encoder/common/gaussian_adapter.py:50-98
+ *   build_covariance / quaternion_to_matrix   src/model/encoder/common/gaussians.py:7-43
+ *   get_world_rays / unproject        src/geometry/projection.py:74-113
+ *   rotate_sh_with_precomputed        src/misc/sh_rotation_optimized.py:56-101
+ * with one kernel forward and one backward, as called from its only call site (encoder_trans.py:307-318): N = b*v
+ * context views, n = rays*surfaces*gaussians_per_pixel Gaussians per view, every per-view quantity broadcast over n.
+ * Outputs are written in the layouts the rasterizer reads (means [N,n,3], covariances [N,n,3,3], harmonics
+ * [N,n,3,d_sh]), i.e. Gaussians{means, covariances, harmonics} after the encoder's rearrange "b v r srf spp -> b (v r
+ * srf spp)" is a pure view.  Opacities pass through unchanged (not an argument).
+ * ------------------------------------------------------------------------------------------------------------ */
+typedef struct TsplatAdapterProblem {
+  int32_t N;          /* context views of the call (batch * views)                                        */
+  int32_t n;          /* Gaussians per view                                                               */
+  int32_t sh_degree;  /* cfg.sh_degree, 0..4; d_sh = (sh_degree + 1)^2                                    */
+  int32_t H, W;       /* image_shape of the context views (pixel size of the scale multiplier, :66-68)    */
+  float scale_min;    /* cfg.gaussian_scale_min                                                           */
+  float scale_max;    /* cfg.gaussian_scale_max                                                           */
+  float eps;          /* forward(..., eps=1e-8): quaternion normalisation (:72)                           */
+  const float* extrinsics;  /* [N,4,4] camera-to-world, row-major                                         */
+  const float* intrinsics;  /* [N,3,3] normalised                                                         */
+  const float* coordinates; /* [N,n,2] ray coordinates in [0,1]^2                                         */
+  const float* depths;      /* [N,n]                                                                      */
+  const float* raw;         /* [N,n,7+3*d_sh] raw_gaussians: scales 3, rotation xyzw 4, sh [3][d_sh]      */
+  const float* wigner;      /* [N, sum_l (2l+1)^2] per-degree Wigner-D blocks, row-major, concatenated
+                               (precompute_wigner_d_matrices, sh_rotation_optimized.py:27-53)             */
+  const float* sh_mask;     /* [d_sh] GaussianAdapter.sh_mask (:36-46)                                    */
+} TsplatAdapterProblem;
+
+/* means [N,n,3], covariances [N,n,3,3], harmonics [N,n,3,d_sh], scales [N,n,3], rotations [N,n,4] (xyzw, normalised) */
+int tsplat_adapter_forward(const TsplatAdapterProblem* p, float* means, float* covariances, float* harmonics,
+                           float* scales, float* rotations, void* cuda_stream);
+/* gradients w.r.t. coordinates [N,n,2], depths [N,n], raw [N,n,7+3*d_sh] from those of means, covariances and
+ * harmonics (scales / rotations are export-only outputs, gaussian_adapter.py:91-94: no gradient path). */
+int tsplat_adapter_backward(const TsplatAdapterProblem* p, const float* dL_dmeans, const float* dL_dcovariances,
+                            const float* dL_dharmonics, float* dL_dcoordinates, float* dL_ddepths, float* dL_draw,
+                            void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

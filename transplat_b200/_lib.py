@@ -20,7 +20,7 @@ DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "lo
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
            "tsplat_backward", "tsplat_mark_visible", "tsplat_pack_cameras", "tsplat_status_read", "tsplat_profile_enable",
-           "tsplat_profile_read")
+           "tsplat_profile_read", "tsplat_adapter_forward", "tsplat_adapter_backward")
 
 
 class TsplatProblem(C.Structure):
@@ -73,6 +73,8 @@ def lib():
         L.tsplat_pack_cameras.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         L.tsplat_status_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_adapter_forward.argtypes = [C.c_void_p] * 7
+        L.tsplat_adapter_backward.argtypes = [C.c_void_p] * 8
         L.tsplat_profile_enable.argtypes = [C.c_int]
         L.tsplat_profile_read.argtypes = [C.c_void_p, C.c_int]
         _lib = L

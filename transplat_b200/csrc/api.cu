@@ -352,4 +352,27 @@ int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* c
   return TSPLAT_OK;
 }
 
+int tsplat_adapter_forward(const TsplatAdapterProblem* p, float* means, float* covariances, float* harmonics,
+                           float* scales, float* rotations, void* cuda_stream) {
+  if (!p) { set_error("adapter_forward: null problem"); return TSPLAT_EINVAL; }
+  int bad = 0;
+  cudaError_t e = tsplat::launch_adapter_forward(*p, means, covariances, harmonics, scales, rotations,
+                                                 static_cast<cudaStream_t>(cuda_stream), &bad);
+  if (bad) { set_error("adapter_forward: bad shape (sh_degree 0..4, H, W > 0) or null pointer"); return TSPLAT_EINVAL; }
+  if (e != cudaSuccess) return cuda_fail("adapter_forward", e);
+  return TSPLAT_OK;
+}
+
+int tsplat_adapter_backward(const TsplatAdapterProblem* p, const float* dL_dmeans, const float* dL_dcovariances,
+                            const float* dL_dharmonics, float* dL_dcoordinates, float* dL_ddepths, float* dL_draw,
+                            void* cuda_stream) {
+  if (!p) { set_error("adapter_backward: null problem"); return TSPLAT_EINVAL; }
+  int bad = 0;
+  cudaError_t e = tsplat::launch_adapter_backward(*p, dL_dmeans, dL_dcovariances, dL_dharmonics, dL_dcoordinates,
+                                                  dL_ddepths, dL_draw, static_cast<cudaStream_t>(cuda_stream), &bad);
+  if (bad) { set_error("adapter_backward: bad shape (sh_degree 0..4, H, W > 0) or null pointer"); return TSPLAT_EINVAL; }
+  if (e != cudaSuccess) return cuda_fail("adapter_backward", e);
+  return TSPLAT_OK;
+}
+
 }  // extern "C"

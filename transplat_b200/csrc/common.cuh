@@ -111,6 +111,11 @@ cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& 
 cudaError_t launch_pack_cameras(int N, const float* extrinsics, const float* intrinsics, const float* near_,
                                 const float* far_, const float* bg, int bg_stride, int scale_invariant,
                                 TsplatCamera* out, cudaStream_t st);
+cudaError_t launch_adapter_forward(const TsplatAdapterProblem& p, float* means, float* cov, float* harmonics,
+                                   float* scales, float* rotations, cudaStream_t st, int* bad);
+cudaError_t launch_adapter_backward(const TsplatAdapterProblem& p, const float* g_means, const float* g_cov,
+                                    const float* g_harm, float* g_coords, float* g_depths, float* g_raw,
+                                    cudaStream_t st, int* bad);
 void launch_status_store(const void* workspace, void* host_alias, cudaStream_t st);
 cudaError_t launch_mark_visible(int G, const float* means, const float* view, uint8_t* present,
                                 cudaStream_t st);
