@@ -137,11 +137,14 @@ def run_ours(args):
     target = target_h[None].to(dev)
     dLd = dLd_h[None].to(dev)
 
+    one = torch.ones((), device=dev)
+
     def step(s):
+        # colour loss = LossMse (loss_mse.py:23-31) fused into the render kernels (forward_mse); depth gets a synthetic
+        # upstream gradient (loss_depth.py's role)
         g = Gaussians(s["means"], s["cov"], s["sh"], s["op"])
-        out = decoder.forward(g, s["ext"], s["intr"], s["near"], s["far"], (HW, HW), depth_mode="depth")
-        dLc = (out.color - target) * (2.0 / numel)  # MSE gradient (loss_mse.py:30-31)
-        return out, torch.autograd.grad([out.color, out.depth], [s["means"], s["cov"], s["sh"], s["op"]], [dLc, dLd])
+        out, loss = decoder.forward_mse(g, s["ext"], s["intr"], s["near"], s["far"], (HW, HW), target, depth_mode="depth")
+        return out, loss, torch.autograd.grad([loss, out.depth], [s["means"], s["cov"], s["sh"], s["op"]], [one, dLd])
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
@@ -231,7 +234,7 @@ def run_ours(args):
                    "parallelism": f"scene-sharded x{world} (no collective)",
                    "l2": "256 MiB buffer zeroed between timed steps (outside the event pairs); "
                          f"{N_SCENES} scenes cycled",
-                   "api": "DecoderSplattingCUDA.forward(depth_mode='depth') + torch.autograd.grad"},
+                   "api": "DecoderSplattingCUDA.forward_mse(depth_mode='depth') [render + fused MSE colour loss] + torch.autograd.grad"},
         "clocks": clocks,
         "e2e": e2e,
         "gpu_launches": args.steps * launches_per_step(VIEWS, T),
@@ -254,13 +257,13 @@ def run_ours(args):
 
 
 def launches_per_step(n_views: int, T: int) -> int:
-    """Kernels of libtsplat.so launched per step (the two torch elementwise kernels of the MSE gradient are not ours).
+    """Kernels of libtsplat.so launched per step (the MSE colour loss runs inside the render kernels).
     bucket path (default): pack_cameras, preprocess_forward, bucket_scan, bucket_emit, tile_sort_gather,
-    big_tile_sort_gather, render_forward, status_store, render_backward, preprocess_backward = 10;
+    big_tile_sort_gather, gather_records, render_forward, status_store, render_backward, preprocess_backward = 11;
     onesweep path: pack_cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd/bwd, preprocess bwd."""
     if os.environ.get("TSPLAT_SORT", "bucket") == "onesweep":
         return 8 + sort_passes(n_views, T)
-    return 10
+    return 11
 
 
 def sort_passes(n_views: int, T: int) -> int:
@@ -305,16 +308,16 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
     lay_grad = SlabLayout(dict(g_means=(1, G, 3), g_cov=(1, G, 3, 3), g_sh=(1, G, 3, 25), g_op=(1, G)))
     n_out = 4  # result buffers cycled (a consumer would read them between steps)
     outs = [dict(images=lay_img.empty_pinned(), grads=lay_grad.empty_pinned()) for _ in range(n_out)]
-    numel = float(VIEWS * 3 * HW * HW)
+    one = torch.ones((), device=dev)
     h2d = host[0]["slab"].numel() * 4
     d2h = sum(t.numel() * 4 for t in outs[0].values())
 
     def step_fn(dv):
         d = lay_in.views(dv["slab"])
         leaves = [d[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
-        out = decoder.forward(Gaussians(*leaves), d["ext"], d["intr"], d["near"], d["far"], (HW, HW), depth_mode="depth")
-        dLc = (out.color - d["target"]) * (2.0 / numel)
-        g = torch.autograd.grad([out.color, out.depth], leaves, [dLc, d["dLd"]])
+        out, loss = decoder.forward_mse(Gaussians(*leaves), d["ext"], d["intr"], d["near"], d["far"], (HW, HW), d["target"],
+                                        depth_mode="depth")
+        g = torch.autograd.grad([loss, out.depth], leaves, [one, d["dLd"]])
         images, grads = flat_images(out.color, out.depth), flat_gradients(*g)
         assert images is not None and images.numel() == lay_img.total and grads.numel() == lay_grad.total
         return dict(images=images, grads=grads)

@@ -174,6 +174,29 @@ int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_
                     float* dL_dmeans, float* dL_dcov, float* dL_dsh, float* dL_dopacity,
                     float* dL_dmeans2D, void* cuda_stream);
 
+/* The step AFTER the render path fused into it: the MSE colour loss of the reference,
+ *   delta = prediction.color - target; loss = weight * (delta ** 2).mean()        src/loss/loss_mse.py:23-31
+ * tsplat_forward_mse = tsplat_forward + the sum of squared differences, accumulated in the render kernel's epilogue
+ * (one partial per (view, tile) CTA, summed in a fixed order by the last CTA: deterministic).  tsplat_backward_mse =
+ * tsplat_backward whose upstream colour gradient is formed in the render-backward prologue:
+ *   dL/dcolor = dL_dcolor (may be NULL) + (*dL_dloss) * scale * (color - target),    scale = 2 * weight / numel,
+ * so neither delta nor dL/dcolor is ever materialised and no elementwise kernel runs between forward and backward. */
+typedef struct TsplatMse {
+  const float* target;   /* [B*V, 3, H, W] ground-truth images (device)                                     */
+  float* loss_sum;       /* forward: 1 float (device) <- loss_scale * sum over views, channels, pixels of delta^2 */
+  const float* color;    /* backward: the out_color written by the forward                                    */
+  const float* dL_dloss; /* backward: 1 float (device), upstream gradient of the loss VALUE                   */
+  float scale;           /* backward: 2 * weight / numel (host)                                               */
+  float loss_scale;      /* forward: weight / numel (host), so *loss_sum is the reference's loss value        */
+} TsplatMse;
+int tsplat_forward_mse(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                       float* out_color, float* out_depth, int32_t* out_radii, const TsplatMse* mse,
+                       void* cuda_stream);
+int tsplat_backward_mse(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                        const float* dL_dcolor, const float* dL_ddepth, float* dL_dmeans, float* dL_dcov,
+                        float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, const TsplatMse* mse,
+                        void* cuda_stream);
+
 /* Replaces _C.mark_visible (GaussianRasterizer.markVisible).  present [G] uint8. */
 int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix,
                         const float* projmatrix, uint8_t* present, void* cuda_stream);

@@ -18,11 +18,15 @@ S = [dict(means=leaf(sc.means), cov=leaf(sc.covariances), sh=leaf(sc.harmonics),
           far=sc.far[None].to(dev)) for sc in scs]
 dec = DecoderSplattingCUDA().to(dev)
 numel = float(V * 3 * HW * HW)
+one = torch.ones((), device=dev)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
 
 
 def step(s):
     g = Gaussians(s["means"], s["cov"], s["sh"], s["op"])
+    if os.environ.get("FUSED", "1") == "1":
+        out, loss = dec.forward_mse(g, s["ext"], s["intr"], s["near"], s["far"], (HW, HW), target, depth_mode="depth")
+        return torch.autograd.grad([loss, out.depth], [s["means"], s["cov"], s["sh"], s["op"]], [one, dLd])
     out = dec.forward(g, s["ext"], s["intr"], s["near"], s["far"], (HW, HW), depth_mode="depth")
     dLc = (out.color - target) * (2.0 / numel)
     return torch.autograd.grad([out.color, out.depth], [s["means"], s["cov"], s["sh"], s["op"]], [dLc, dLd])

@@ -76,6 +76,51 @@ view0 = sc.extrinsics[0].inverse().T.contiguous()
 out["visible_view0"] = torch.from_numpy(mark_visible(sc.means.numpy(), view0.numpy()).astype(np.uint8))
 out["visible_viewmatrix"] = view0
 
+# --- the step after the path: the UNMODIFIED LossMse (src/loss/loss_mse.py:21-31) on the reference's render_cuda output
+import importlib.util  # noqa: E402
+
+
+def load_loss_mse(ref_root="/root/reference"):
+    saved = {k: v for k, v in sys.modules.items() if k == "src" or k.startswith("src.") or k == "jaxtyping"}
+    for k in saved:
+        del sys.modules[k]
+    try:
+        jt = types.ModuleType("jaxtyping")
+        jt.Float = type("Float", (), {"__class_getitem__": classmethod(lambda cls, item: cls)})
+        sys.modules["jaxtyping"] = jt
+        for name, attrs in (("src", ()), ("src.loss", ()), ("src.dataset", ()), ("src.model", ()), ("src.model.decoder", ()),
+                            ("src.dataset.types", ("BatchedExample",)), ("src.model.decoder.decoder", ("DecoderOutput",)),
+                            ("src.model.types", ("Gaussians",))):
+            m = types.ModuleType(name)
+            m.__path__ = [f"{ref_root}/{name.replace('.', '/')}"]
+            for a in attrs:
+                setattr(m, a, object)
+            sys.modules[name] = m
+        mods = {}
+        for name in ("src.loss.loss", "src.loss.loss_mse"):
+            spec = importlib.util.spec_from_file_location(name, f"{ref_root}/{name.replace('.', '/')}.py")
+            mods[name] = importlib.util.module_from_spec(spec)
+            sys.modules[name] = mods[name]
+            spec.loader.exec_module(mods[name])
+        return mods["src.loss.loss_mse"]
+    finally:
+        for k in list(sys.modules):
+            if k == "src" or k.startswith("src.") or k == "jaxtyping":
+                del sys.modules[k]
+        sys.modules.update(saved)
+
+
+lm = load_loss_mse()
+loss_fn = lm.LossMse(lm.LossMseCfgWrapper(lm.LossMseCfg(weight=0.7)))
+means_r, cov_r, sh_r, op_r = rep(sc.means), rep(cov), rep(sh), rep(sc.opacities)
+img = ref.render_cuda(sc.extrinsics, sc.intrinsics, sc.near, sc.far, (H, W), bg[None].expand(V, 3), means_r, cov_r, sh_r, op_r)
+target = torch.rand(1, V, 3, H, W, generator=g)
+pred = types.SimpleNamespace(color=img[None])
+loss = loss_fn.forward(pred, {"target": {"image": target}}, None, 0)
+loss.backward()
+out.update(mse_target=target[0], mse_weight=torch.tensor(0.7), mse_loss=loss.detach(), mse_g_means=means_r.grad.sum(0),
+           mse_g_cov=cov_r.grad.sum(0), mse_g_sh=sh_r.grad.sum(0), mse_g_op=op_r.grad.sum(0))
+
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_host_variants.npz")
 np.savez_compressed(path, **{k: (v.numpy() if torch.is_tensor(v) else v) for k, v in out.items()})
 print("wrote", path, os.path.getsize(path), "bytes;", "visible", out["stats_visible"].tolist(), "high", out["stats_high"].tolist(),

@@ -121,7 +121,11 @@ def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=Tru
         if grads[4] is not None:
             ref2d = np.stack([st.extra["mean2d"] for st in states])
             bwd["mean2d_rel"] = rel_err(grads[4].cpu().numpy().astype(np.float64), ref2d)
-        acc_gpu = inspect_workspace(state)["grad_acc"].cpu().numpy().astype(np.float64)
+        ins = inspect_workspace(state)
+        acc_gpu = ins["grad_acc"].cpu().numpy().astype(np.float64)
         scr = np.stack([st.extra["screen"] for st in states])
+        # accumulators of culled Gaussians (radius 0) are never initialised nor read (preprocess.cu / preprocess_bwd.cu)
+        vis = (ins["radii"].cpu().numpy() > 0)[..., None]
+        acc_gpu, scr = np.where(vis, acc_gpu, 0.0), np.where(vis, scr[..., :acc_gpu.shape[-1]], 0.0)
         bwd["screen_rel"] = max(rel_err(acc_gpu[..., k], scr[..., k]) for k in range(10 if cfg.depth_mode else 9))
     return fwd, bwd

@@ -335,3 +335,33 @@ def test_golden_mark_visible():
                                       False, False)
     got = GaussianRasterizer(s).markVisible(t("means")).cpu().numpy().astype(np.uint8)
     assert np.array_equal(got, zv["visible_view0"])
+
+
+def test_golden_fused_mse_loss():
+    """forward_mse (loss in the render-forward epilogue, dL/dcolor formed in the render-backward prologue) against the
+    UNMODIFIED LossMse (src/loss/loss_mse.py:21-31) applied to the reference's render_cuda output, and against the
+    unfused path of this library; the loss value is deterministic (fixed summation order)."""
+    from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+    z, t, zv, tv = _gold_var()
+    H, W = z["color"].shape[-2:]
+    dec = DecoderSplattingCUDA(background_color=tuple(z["bg"].tolist())).cuda()
+    cam = (t("extrinsics")[None], t("intrinsics")[None], t("near")[None], t("far")[None])
+    target = tv("mse_target")[None]
+    w = float(zv["mse_weight"])
+    leaves = [t(k).unsqueeze(0).requires_grad_(True) for k in ("means", "cov", "harmonics", "opacities")]
+    out, loss = dec.forward_mse(Gaussians(*leaves), *cam, (H, W), target, weight=w)
+    assert loss.dim() == 0 and abs(float(loss) - float(zv["mse_loss"])) <= 2e-6 * float(zv["mse_loss"])
+    assert np.abs(out.color[0].detach().cpu().numpy() - z["color"]).max() <= COLOR_ATOL
+    loss.backward()
+    for leaf, k in zip(leaves, ("mse_g_means", "mse_g_cov", "mse_g_sh", "mse_g_op")):
+        assert _rel(leaf.grad[0], zv[k]) <= GRAD_RTOL, k
+    # fused + another loss on colour and depth == unfused composition; and run-to-run identical loss bits
+    l2 = [x.detach().clone().requires_grad_(True) for x in leaves]
+    out2, loss2 = dec.forward_mse(Gaussians(*l2), *cam, (H, W), target, depth_mode="depth", weight=w)
+    assert float(loss2) == float(loss)
+    (3.0 * loss2 + (out2.color * t("w_color")).sum() + (out2.depth[0] * t("w_depth")).sum()).backward()
+    l3 = [x.detach().clone().requires_grad_(True) for x in leaves]
+    out3 = dec.forward(Gaussians(*l3), *cam, (H, W), depth_mode="depth")
+    (3.0 * w * ((out3.color - target) ** 2).mean() + (out3.color * t("w_color")).sum() + (out3.depth[0] * t("w_depth")).sum()).backward()
+    for a, b in zip(l2, l3):
+        assert _rel(a.grad, b.grad.cpu().numpy()) <= 1e-5

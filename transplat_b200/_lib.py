@@ -20,7 +20,8 @@ DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "lo
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
            "tsplat_backward", "tsplat_mark_visible", "tsplat_pack_cameras", "tsplat_status_read", "tsplat_profile_enable",
-           "tsplat_profile_read", "tsplat_adapter_forward", "tsplat_adapter_backward")
+           "tsplat_profile_read", "tsplat_adapter_forward", "tsplat_adapter_backward", "tsplat_forward_mse",
+           "tsplat_backward_mse")
 
 
 class TsplatProblem(C.Structure):
@@ -34,6 +35,11 @@ class TsplatLayout(C.Structure):
         "total_bytes", "status", "depths", "radii", "xy", "conic_opacity", "rgbd", "tiles_touched",
         "clamped", "keys", "vals", "ranges", "final_T", "n_contrib", "grad_acc")] + [
         (n, C.c_int32) for n in ("tiles_x", "tiles_y", "sort_bits", "sort_passes", "rec_stride", "reserved0")]
+
+
+class TsplatMse(C.Structure):
+    _fields_ = [("target", C.c_void_p), ("loss_sum", C.c_void_p), ("color", C.c_void_p), ("dL_dloss", C.c_void_p),
+                ("scale", C.c_float), ("loss_scale", C.c_float)]
 
 
 class TsplatStatus(C.Structure):
@@ -73,6 +79,11 @@ def lib():
         L.tsplat_pack_cameras.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                           C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]
         L.tsplat_status_read.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.tsplat_forward_mse.argtypes = [C.POINTER(TsplatProblem), C.c_void_p, C.c_uint64, C.c_uint64,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(TsplatMse), C.c_void_p]
+        L.tsplat_backward_mse.argtypes = [C.POINTER(TsplatProblem), C.c_void_p, C.c_uint64, C.c_uint64,
+                                          C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                          C.c_void_p, C.c_void_p, C.POINTER(TsplatMse), C.c_void_p]
         L.tsplat_adapter_forward.argtypes = [C.c_void_p] * 7
         L.tsplat_adapter_backward.argtypes = [C.c_void_p] * 8
         L.tsplat_profile_enable.argtypes = [C.c_int]

@@ -99,6 +99,7 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   L.n_contrib = take(4 * N * P);
   // ---- backward ----
   L.grad_acc = take(4ull * kAccFloats * NG);
+  out->loss_partial = take(4ull * N * T);
   L.total_bytes = off;
   return TSPLAT_OK;
 }
@@ -122,6 +123,7 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   w.final_T = reinterpret_cast<float*>(b + L.final_T);
   w.n_contrib = reinterpret_cast<unsigned int*>(b + L.n_contrib);
   w.grad_acc = reinterpret_cast<float*>(b + L.grad_acc);
+  w.loss_partial = reinterpret_cast<float*>(b + F.loss_partial);
   w.rec0 = reinterpret_cast<float4*>(b + F.rec0);
   w.rec1 = reinterpret_cast<float4*>(b + F.rec1);
   w.rec2 = reinterpret_cast<float4*>(b + F.rec2);
@@ -209,8 +211,9 @@ int tsplat_workspace_layout(const TsplatProblem* p, uint64_t d_cap, TsplatLayout
   return TSPLAT_OK;
 }
 
-int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
-                   float* out_color, float* out_depth, int32_t* out_radii, void* cuda_stream) {
+static int forward_impl(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                        float* out_color, float* out_depth, int32_t* out_radii, const TsplatMse* mse,
+                        void* cuda_stream) {
   LayoutFull F;
   Workspace ws;
   int rc = prepare(p, workspace, workspace_bytes, d_cap, &F, &ws);
@@ -251,19 +254,32 @@ int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_b
       if (e != cudaSuccess) return cuda_fail("ranges_gather", e);
     }
   }
-  { StageTimer t(kStRender, st); e = launch_render_forward(*p, ws, out_color, out_depth, st); }
+  { StageTimer t(kStRender, st); e = launch_render_forward(*p, ws, out_color, out_depth, mse, st); }
   if (e != cudaSuccess) return cuda_fail("render_forward", e);
   return TSPLAT_OK;
 }
 
-int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
-                    const float* dL_dcolor, const float* dL_ddepth, float* dL_dmeans, float* dL_dcov,
-                    float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, void* cuda_stream) {
+int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                   float* out_color, float* out_depth, int32_t* out_radii, void* cuda_stream) {
+  return forward_impl(p, workspace, workspace_bytes, d_cap, out_color, out_depth, out_radii, nullptr, cuda_stream);
+}
+
+int tsplat_forward_mse(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                       float* out_color, float* out_depth, int32_t* out_radii, const TsplatMse* mse,
+                       void* cuda_stream) {
+  if (!mse || !mse->target || !mse->loss_sum) { set_error("forward_mse: target and loss_sum are required"); return TSPLAT_EINVAL; }
+  return forward_impl(p, workspace, workspace_bytes, d_cap, out_color, out_depth, out_radii, mse, cuda_stream);
+}
+
+static int backward_impl(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                         const float* dL_dcolor, const float* dL_ddepth, float* dL_dmeans, float* dL_dcov,
+                         float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, const TsplatMse* mse,
+                         void* cuda_stream) {
   LayoutFull F;
   Workspace ws;
   int rc = prepare(p, workspace, workspace_bytes, d_cap, &F, &ws);
   if (rc) return rc;
-  if (!dL_dcolor || !dL_dmeans || !dL_dcov || !dL_dsh || !dL_dopacity) { set_error("NULL gradient pointer"); return TSPLAT_EINVAL; }
+  if ((!dL_dcolor && !mse) || !dL_dmeans || !dL_dcov || !dL_dsh || !dL_dopacity) { set_error("NULL gradient pointer"); return TSPLAT_EINVAL; }
   if (p->depth_mode != TSPLAT_DEPTH_NONE && !dL_ddepth) { set_error("depth_mode set but dL_ddepth is NULL"); return TSPLAT_EINVAL; }
   if (p->G == 0) return TSPLAT_OK;
   cudaStream_t st = static_cast<cudaStream_t>(cuda_stream);
@@ -275,7 +291,7 @@ int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_
     e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * (uint64_t)p->B * p->V * p->G, st);
     if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
   }
-  { StageTimer t(kStRenderB, st); e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, st); }
+  { StageTimer t(kStRenderB, st); e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, mse, st); }
   if (e != cudaSuccess) return cuda_fail("render_backward", e);
   {
     StageTimer t(kStPreB, st);
@@ -283,6 +299,25 @@ int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_
   }
   if (e != cudaSuccess) return cuda_fail("preprocess_backward", e);
   return TSPLAT_OK;
+}
+
+int tsplat_backward(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                    const float* dL_dcolor, const float* dL_ddepth, float* dL_dmeans, float* dL_dcov,
+                    float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, void* cuda_stream) {
+  return backward_impl(p, workspace, workspace_bytes, d_cap, dL_dcolor, dL_ddepth, dL_dmeans, dL_dcov, dL_dsh,
+                       dL_dopacity, dL_dmeans2D, nullptr, cuda_stream);
+}
+
+int tsplat_backward_mse(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
+                        const float* dL_dcolor, const float* dL_ddepth, float* dL_dmeans, float* dL_dcov,
+                        float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, const TsplatMse* mse,
+                        void* cuda_stream) {
+  if (!mse || !mse->target || !mse->color || !mse->dL_dloss) {
+    set_error("backward_mse: target, color and dL_dloss are required");
+    return TSPLAT_EINVAL;
+  }
+  return backward_impl(p, workspace, workspace_bytes, d_cap, dL_dcolor, dL_ddepth, dL_dmeans, dL_dcov, dL_dsh,
+                       dL_dopacity, dL_dmeans2D, mse, cuda_stream);
 }
 
 int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix, const float* projmatrix,

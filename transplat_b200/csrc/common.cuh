@@ -46,7 +46,7 @@ struct Control {
   unsigned int sort_tile_counter[kMaxPasses];
   unsigned int gather_done;         // CTAs of ranges_gather that have finished (last one orders the tiles)
   unsigned int num_big;             // bucket path: tiles whose list does not fit the small-tile sort kernel
-  unsigned int pad[1];
+  unsigned int loss_done;           // CTAs of render_forward that have written their MSE partial (fused loss)
   unsigned int hist[kMaxPasses][kRadix];  // global digit histograms (onesweep: one upfront sweep)
 };
 
@@ -65,6 +65,7 @@ struct Workspace {
   float* final_T;
   unsigned int* n_contrib;
   float* grad_acc;
+  float* loss_partial;             // fused MSE loss: one partial sum per (view, tile) CTA of render_forward
   float4* rec0;  // x, y, conic.x, conic.y                      (sorted order)
   float4* rec1;  // conic.z, opacity, r, g
   float4* rec2;  // b, depth feature, bits(Gaussian id), cull threshold tau_s (cull.cuh)
@@ -84,7 +85,7 @@ struct Workspace {
 
 struct LayoutFull {
   TsplatLayout pub;
-  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, scan_state, sort_state, tile_order, tile_count, tile_cursor, big_list,
+  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, loss_partial, scan_state, sort_state, tile_order, tile_count, tile_cursor, big_list,
       zero_begin, zero_mid, zero_end;  // [zero_begin, zero_mid) is all the bucket path needs cleared
   int num_scan_tiles, num_sort_tiles;
 };
@@ -102,9 +103,9 @@ cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStr
 cudaError_t launch_sort(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_ranges_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color,
-                                  float* out_depth, cudaStream_t st);
+                                  float* out_depth, const TsplatMse* mse, cudaStream_t st);
 cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,
-                                   const float* dL_ddepth, cudaStream_t st);
+                                   const float* dL_ddepth, const TsplatMse* mse, cudaStream_t st);
 cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& ws, float* dL_dmeans,
                                        float* dL_dcov, float* dL_dsh, float* dL_dopacity,
                                        float* dL_dmeans2D, cudaStream_t st);

@@ -30,6 +30,7 @@ struct RingSmem {
   uint64_t full[kStages];
   uint64_t empty[kStages];
   int done_warps;
+  float red[kConsumerWarps];  // fused MSE loss: per-warp partial sums
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -94,7 +95,9 @@ template <int CH>
 __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspace ws, int H, int W,
                                                                         const TsplatCamera* __restrict__ cams,
                                                                         float* __restrict__ out_color,
-                                                                        float* __restrict__ out_depth) {
+                                                                        float* __restrict__ out_depth,
+                                                                        const float* __restrict__ target,
+                                                                        float* __restrict__ loss_sum, float loss_scale) {
   __shared__ __align__(128) RingSmem s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int bid = ws.use_order ? (int)ws.tile_order[blockIdx.x] : (int)blockIdx.x;  // longest lists first
@@ -205,18 +208,53 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
     if (lane == 0) mbar_arrive(&s.empty[st]);
     if (warp_done && ld_volatile_smem(&s.done_warps) == kConsumerWarps) break;
   }
+  float sq = 0.0f;  // fused MSE (loss_mse.py:30): this pixel's sum over channels of (colour - target)^2
   if (inside) {
     const size_t pix = (size_t)py * W + px;
     const size_t P = (size_t)H * W;
     const float* bg = cams[n].bg;
     ws.final_T[n * P + pix] = T;
     ws.n_contrib[n * P + pix] = last_contributor;
-    out_color[(n * 3 + 0) * P + pix] = C[0] + T * __ldg(bg + 0);
-    out_color[(n * 3 + 1) * P + pix] = C[1] + T * __ldg(bg + 1);
-    out_color[(n * 3 + 2) * P + pix] = C[2] + T * __ldg(bg + 2);
+    const float c0 = C[0] + T * __ldg(bg + 0), c1 = C[1] + T * __ldg(bg + 1), c2 = C[2] + T * __ldg(bg + 2);
+    out_color[(n * 3 + 0) * P + pix] = c0;
+    out_color[(n * 3 + 1) * P + pix] = c1;
+    out_color[(n * 3 + 2) * P + pix] = c2;
     if (CH == 4) {  // mean over three identical channels (cuda_splatting.py:417)
       const float x = C[3];
       out_depth[n * P + pix] = __fdiv_rn(__fadd_rn(__fadd_rn(x, x), x), 3.0f);
+    }
+    if (target != nullptr) {
+      const float d0 = c0 - target[(n * 3 + 0) * P + pix], d1 = c1 - target[(n * 3 + 1) * P + pix],
+                  d2 = c2 - target[(n * 3 + 2) * P + pix];
+      sq = d0 * d0 + d1 * d1 + d2 * d2;
+    }
+  }
+  if (target != nullptr) {
+    // CTA partial in a fixed order; the LAST CTA to finish adds all partials in index order: the loss value does
+    // not depend on the order in which the tiles complete
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    if (lane == 0) s.red[warp] = sq;
+    asm volatile("bar.sync 1, %0;" ::"r"(kTilePix) : "memory");  // the 8 consumer warps (the producer has left)
+    if (warp == 0) {
+      unsigned int last = 0;
+      if (lane == 0) {
+        float t = 0.0f;
+#pragma unroll
+        for (int i = 0; i < kConsumerWarps; i++) t += s.red[i];
+        ws.loss_partial[bid] = t;
+        __threadfence();
+        last = atomicAdd(&ws.ctl->loss_done, 1u) == gridDim.x - 1 ? 1u : 0u;
+      }
+      last = __shfl_sync(0xffffffffu, last, 0);
+      if (last) {
+        __threadfence();
+        float t = 0.0f;
+        for (unsigned int i = lane; i < gridDim.x; i += 32) t += __ldcg(ws.loss_partial + i);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+        if (lane == 0) *loss_sum = t * loss_scale;
+      }
     }
   }
 }
@@ -337,7 +375,8 @@ template <int CH>
 __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspace ws, int H, int W, int G,
                                                                          const TsplatCamera* __restrict__ cams,
                                                                          const float* __restrict__ dL_dcolor,
-                                                                         const float* __restrict__ dL_ddepth) {
+                                                                         const float* __restrict__ dL_ddepth,
+                                                                         TsplatMse mse) {
   extern __shared__ __align__(128) unsigned char bsmem_raw[];
   RingBwdSmem& s = *reinterpret_cast<RingBwdSmem*>(bsmem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -398,8 +437,16 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
 #pragma unroll
   for (int ch = 0; ch < CH; ch++) { accum_rec[ch] = 0.0f; last_color[ch] = 0.0f; dL_dpix[ch] = 0.0f; }
   if (inside) {
+    if (dL_dcolor != nullptr) {
 #pragma unroll
-    for (int ch = 0; ch < 3; ch++) dL_dpix[ch] = dL_dcolor[(n * 3 + ch) * P + pix];
+      for (int ch = 0; ch < 3; ch++) dL_dpix[ch] = dL_dcolor[(n * 3 + ch) * P + pix];
+    }
+    if (mse.target != nullptr) {  // fused MSE: dL/dcolor += dL/dloss * 2 w / numel * (colour - target)
+      const float gl = __ldg(mse.dL_dloss) * mse.scale;
+#pragma unroll
+      for (int ch = 0; ch < 3; ch++)
+        dL_dpix[ch] += gl * (mse.color[(n * 3 + ch) * P + pix] - mse.target[(n * 3 + ch) * P + pix]);
+    }
     if (CH == 4) dL_dpix[3] = dL_ddepth[n * P + pix];
   }
   const float* bgp = cams[n].bg;
@@ -495,30 +542,35 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
 }
 
 cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color, float* out_depth,
-                                  cudaStream_t st) {
+                                  const TsplatMse* mse, cudaStream_t st) {
   const int grid = ws.N * ws.T;
   if (grid == 0) return cudaSuccess;
+  const float* target = mse ? mse->target : nullptr;
+  float* loss_sum = mse ? mse->loss_sum : nullptr;
+  const float loss_scale = mse ? mse->loss_scale : 0.0f;
   if (p.depth_mode != TSPLAT_DEPTH_NONE)
-    render_forward_kernel<4><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
+    render_forward_kernel<4><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth, target, loss_sum, loss_scale);
   else
-    render_forward_kernel<3><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth);
+    render_forward_kernel<3><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth, target, loss_sum, loss_scale);
   return cudaGetLastError();
 }
 
 cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,
-                                   const float* dL_ddepth, cudaStream_t st) {
+                                   const float* dL_ddepth, const TsplatMse* mse_in, cudaStream_t st) {
   const int grid = ws.N * ws.T;
   if (grid == 0) return cudaSuccess;
+  TsplatMse mse{};
+  if (mse_in) mse = *mse_in;
   const int smem = (int)sizeof(RingBwdSmem);
   cudaError_t e;
   if (p.depth_mode != TSPLAT_DEPTH_NONE) {
     e = cudaFuncSetAttribute(render_backward_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    render_backward_kernel<4><<<grid, kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
+    render_backward_kernel<4><<<grid, kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth, mse);
   } else {
     e = cudaFuncSetAttribute(render_backward_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
-    render_backward_kernel<3><<<grid, kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth);
+    render_backward_kernel<3><<<grid, kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth, mse);
   }
   return cudaGetLastError();
 }

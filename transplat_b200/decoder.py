@@ -27,7 +27,7 @@ from torch import Tensor, nn
 
 from ._lib import COV_FULL9, DEPTH_MODES, SH_G3M
 from .cameras import _inverse, get_projection_matrix, pack_cameras_device, pack_cameras_explicit
-from .rasterize import RenderConfig, rasterize
+from .rasterize import RenderConfig, rasterize, rasterize_mse
 
 DepthRenderingMode = Literal["depth", "log", "disparity", "relative_disparity"]
 
@@ -61,8 +61,11 @@ class GaussianContributionStats:
 def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
                  image_shape: tuple, background_color: Tensor, depth_mode: Optional[str] = None,
                  scale_invariant: bool = True, want_radii: bool = False, check: Optional[str] = None,
-                 use_sh: bool = True, cams: Optional[Tensor] = None):
-    """The batched entry point.  extrinsics [b,v,4,4], intrinsics [b,v,3,3], near/far [b,v],
+                 use_sh: bool = True, cams: Optional[Tensor] = None, mse_target: Optional[Tensor] = None,
+                 mse_weight: float = 1.0):
+    """The batched entry point.  With ``mse_target`` [b,v,3,h,w] a fourth value is returned: the reference's MSE colour
+    loss ``mse_weight * ((color - target) ** 2).mean()`` (loss_mse.py:23-31), computed inside the render kernels.
+  extrinsics [b,v,4,4], intrinsics [b,v,3,3], near/far [b,v],
     background_color [3] or [b*v,3].  Returns colour [b,v,3,h,w], depth [b,v,h,w]|None, radii [b,v,G]|None."""
     b, v = extrinsics.shape[:2]
     h, w = image_shape
@@ -79,10 +82,17 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
                        depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check)
     # use_sh=False: the single coefficient is the colour itself (colors_precomp = shs[:, 0, :], cuda_splatting.py:130)
     feat = gaussians.harmonics if use_sh else gaussians.harmonics[..., 0]
-    color, depth, radii = rasterize(gaussians.means, gaussians.covariances, feat, gaussians.opacities, cams, cfg)
+    loss = None
+    if mse_target is not None:
+        color, depth, radii, loss = rasterize_mse(gaussians.means, gaussians.covariances, feat, gaussians.opacities,
+                                                  cams, cfg, mse_target.reshape(b * v, 3, h, w), mse_weight)
+    else:
+        color, depth, radii = rasterize(gaussians.means, gaussians.covariances, feat, gaussians.opacities, cams, cfg)
     color = color.reshape(b, v, 3, h, w)
     depth = depth.reshape(b, v, h, w) if depth is not None else None
     radii = radii.reshape(b, v, -1) if radii is not None else None
+    if mse_target is not None:
+        return color, depth, radii, loss
     return color, depth, radii
 
 
@@ -197,6 +207,17 @@ class DecoderSplattingCUDA(nn.Module):
         color, depth, _ = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
                                        self.background_color, depth_mode)
         return DecoderOutput(color, depth)
+
+    def forward_mse(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
+                    image_shape: tuple, target_image: Tensor, depth_mode: Optional[DepthRenderingMode] = None,
+                    weight: float = 1.0):
+        """forward() + LossMse (src/loss/loss_mse.py:23-31: ``weight * ((prediction.color - batch["target"]["image"])
+        ** 2).mean()``) fused into the render kernels: returns (DecoderOutput, loss).  Backpropagating the loss never
+        materialises the colour difference or its gradient."""
+        color, depth, _, loss = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
+                                             self.background_color, depth_mode, mse_target=target_image,
+                                             mse_weight=weight)
+        return DecoderOutput(color, depth), loss
 
     def render_depth(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
                      image_shape: tuple, mode: DepthRenderingMode = "depth") -> Tensor:

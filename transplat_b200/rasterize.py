@@ -14,7 +14,7 @@ from dataclasses import dataclass
 import torch
 
 from . import _lib
-from ._lib import COV_FULL9, COV_TRIU6, DEPTH_MODES, SH_G3M, SH_GM3, TsplatLayout, TsplatProblem, TsplatStatus
+from ._lib import COV_FULL9, COV_TRIU6, DEPTH_MODES, SH_G3M, SH_GM3, TsplatLayout, TsplatMse, TsplatProblem, TsplatStatus
 
 # capacity of the (tile, Gaussian) pair list, in pairs per (view, Gaussian); grows when a call
 # reports that it came close (see _Capacity)
@@ -130,7 +130,8 @@ def _problem(cfg: RenderConfig, means, cov, sh, opacity, cams) -> TsplatProblem:
 
 class _State:
     """What backward needs from forward: the opaque workspace and the problem description."""
-    __slots__ = ("problem", "workspace", "d_cap", "layout", "key", "tensors", "status_host", "event", "bwd_calls")
+    __slots__ = ("problem", "workspace", "d_cap", "layout", "key", "tensors", "status_host", "event", "bwd_calls",
+                 "mse")  # mse: (target, color, weight/numel factor) of a fused-loss forward, else None
 
 
 def _check_inputs(means, cov, sh, opacity, cams, cfg):
@@ -153,8 +154,10 @@ def _check_inputs(means, cov, sh, opacity, cams, cfg):
         raise RuntimeError(f"cameras must have shape {(B * cfg.V, 64)}, got {tuple(cams.shape)}")
 
 
-def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
-    """Launch the forward pipeline; returns (color, depth|None, radii|None, state)."""
+def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=None, mse_weight: float = 1.0):
+    """Launch the forward pipeline; returns (color, depth|None, radii|None, state).  With ``mse_target`` [N,3,H,W] the
+    render kernel's epilogue also accumulates the reference's MSE loss (loss_mse.py:23-31); it is returned as
+    ``state.mse[3]`` (a 1-element device tensor) and consumed by backward_raw."""
     L = _lib.lib()
     _check_inputs(means, cov, sh, opacity, cams, cfg)
     means, cov, sh, opacity, cams = (t.contiguous() for t in (means, cov, sh, opacity, cams))
@@ -179,9 +182,22 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
             color = images[:n_col].view(N, 3, cfg.H, cfg.W)
             depth = images[_pad64(n_col):_pad64(n_col) + n_dep].view(N, cfg.H, cfg.W) if cfg.depth_mode else None
             radii = torch.empty((N, G), dtype=torch.int32, device=dev) if cfg.want_radii else None
-            _lib.check(L.tsplat_forward(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
-                                        _ptr(depth), _ptr(radii), C.c_void_p(stream.cuda_stream)),
-                       "tsplat_forward")
+            loss = None
+            if mse_target is not None:
+                if tuple(mse_target.shape) != (N, 3, cfg.H, cfg.W) or mse_target.dtype != torch.float32 or \
+                        mse_target.device != dev:
+                    raise RuntimeError(f"mse_target must be float32 {(N, 3, cfg.H, cfg.W)} on {dev}")
+                mse_target = mse_target.contiguous()
+                loss = torch.empty(1, dtype=torch.float32, device=dev)
+                m = TsplatMse(target=mse_target.data_ptr(), loss_sum=loss.data_ptr(), color=0, dL_dloss=0, scale=0.0,
+                              loss_scale=mse_weight / float(n_col))
+                _lib.check(L.tsplat_forward_mse(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
+                                                _ptr(depth), _ptr(radii), C.byref(m), C.c_void_p(stream.cuda_stream)),
+                           "tsplat_forward_mse")
+            else:
+                _lib.check(L.tsplat_forward(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
+                                            _ptr(depth), _ptr(radii), C.c_void_p(stream.cuda_stream)),
+                           "tsplat_forward")
             host = torch.empty(16, dtype=torch.uint8, pin_memory=True)
             _lib.check(L.tsplat_status_read(_ptr(ws), C.c_void_p(host.data_ptr()),
                                             C.c_void_p(stream.cuda_stream)), "tsplat_status_read")
@@ -205,6 +221,7 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams):
     state.tensors = (means, cov, sh, opacity, cams)
     state.status_host, state.event = host, event
     state.bwd_calls = 0
+    state.mse = (mse_target, color, 2.0 * mse_weight / float(color.numel()), loss) if mse_target is not None else None
     return color, depth, radii, state
 
 
@@ -213,7 +230,7 @@ def read_status(state) -> TsplatStatus:
     return TsplatStatus.from_buffer_copy(state.status_host.numpy().tobytes())
 
 
-def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
+def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=None):
     L = _lib.lib()
     means, cov, sh, opacity, cams = state.tensors
     if _capacity.unchecked:
@@ -233,8 +250,11 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
     N = means.shape[0] * cfg.V
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev)
-        grad_color = grad_color.contiguous() if grad_color is not None else torch.zeros(
-            (N, 3, cfg.H, cfg.W), dtype=torch.float32, device=dev)
+        fused = state.mse is not None and grad_loss is not None
+        if grad_color is not None:
+            grad_color = grad_color.contiguous()
+        elif not fused:
+            grad_color = torch.zeros((N, 3, cfg.H, cfg.W), dtype=torch.float32, device=dev)
         if cfg.depth_mode:
             grad_depth = grad_depth.contiguous() if grad_depth is not None else torch.zeros(
                 (N, cfg.H, cfg.W), dtype=torch.float32, device=dev)
@@ -256,10 +276,20 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth):
         if state.bwd_calls:
             state.problem.flags |= _lib.FLAG_REZERO_GRAD_ACC
         state.bwd_calls += 1
-        _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
-                                     state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
-                                     _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
-                   "tsplat_backward")
+        if fused:
+            target, color, scale, _ = state.mse
+            grad_loss = grad_loss.reshape(1).to(torch.float32).contiguous()
+            m = TsplatMse(target=target.data_ptr(), loss_sum=0, color=color.data_ptr(), dL_dloss=grad_loss.data_ptr(),
+                          scale=scale, loss_scale=0.0)
+            _lib.check(L.tsplat_backward_mse(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
+                                             state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means),
+                                             _ptr(g_cov), _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.byref(m),
+                                             C.c_void_p(stream.cuda_stream)), "tsplat_backward_mse")
+        else:
+            _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
+                                         state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
+                                         _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
+                       "tsplat_backward")
     return g_means, g_cov, g_sh, g_op, g_m2d
 
 
@@ -286,6 +316,40 @@ class _Rasterize(torch.autograd.Function):
         if ctx.has_m2d and g_m2d is not None:
             g_m2d = g_m2d.reshape(ctx.m2d_shape)
         return g_means, g_cov, g_sh, g_op, (g_m2d if ctx.has_m2d else None), None, None
+
+
+class _RasterizeMse(torch.autograd.Function):
+    """Render + the reference's MSE colour loss (src/loss/loss_mse.py:23-31) in the same kernels:
+    the loss value comes out of the render-forward epilogue, and the backward forms dL/dcolor = dL_dcolor +
+    dL/dloss * 2 w / numel * (colour - target) in the render-backward prologue - no elementwise kernel in between."""
+
+    @staticmethod
+    def forward(ctx, means, cov, sh, opacity, cams, cfg, target, weight):
+        color, depth, radii, state = forward_raw(cfg, means, cov, sh, opacity, cams, mse_target=target,
+                                                 mse_weight=float(weight))
+        ctx.cfg, ctx.state = cfg, state
+        ctx.set_materialize_grads(False)
+        outs = [color, depth if depth is not None else torch.empty(0, device=color.device),
+                radii if radii is not None else torch.empty(0, dtype=torch.int32, device=color.device),
+                state.mse[3].reshape(())]
+        ctx.mark_non_differentiable(outs[2])
+        if depth is None:
+            ctx.mark_non_differentiable(outs[1])
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_depth, _grad_radii, grad_loss):
+        cfg = ctx.cfg
+        g_means, g_cov, g_sh, g_op, _ = backward_raw(cfg, ctx.state, grad_color,
+                                                     grad_depth if cfg.depth_mode else None, grad_loss=grad_loss)
+        return g_means, g_cov, g_sh, g_op, None, None, None, None
+
+
+def rasterize_mse(means, cov, sh, opacity, cams, cfg: RenderConfig, target, weight: float = 1.0):
+    """rasterize() + loss = weight * ((color - target) ** 2).mean() computed inside the render kernels.
+    target [B*V,3,H,W].  Returns color, depth|None, radii|None, loss (0-d tensor)."""
+    color, depth, radii, loss = _RasterizeMse.apply(means, cov, sh, opacity, cams, cfg, target, weight)
+    return color, (depth if cfg.depth_mode else None), (radii if cfg.want_radii else None), loss
 
 
 def _pad64(n: int) -> int:
