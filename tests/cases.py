@@ -29,6 +29,15 @@ def case(name: str):
     if name == "dense_big":        # few tiles, very long lists: > 4096 and > 16384 pairs per tile (big-tile sort paths)
         sc = make_scene(n_ctx=1, h=144, w=144, n_views=2, render_hw=(32, 48), seed=31)
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=120.0, bg=(0.0, 0.0, 0.0))
+    if name == "c4_dtu":           # BASELINE config 4a: DTU, 3 context views -> 196608 Gaussians, 1 target view, depth
+        sc = make_scene(n_ctx=3, h=256, w=256, n_views=1, seed=41, near=2.125, far=4.525, d0=2.2, d1=4.4)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))
+    if name == "coplanar":         # every Gaussian at the same depth in every view: all sort keys of a tile tie, the
+        # distribution sort bails out and the stable radix fallback must return Gaussian order
+        sc = make_scene(n_ctx=1, h=96, w=96, n_views=2, render_hw=(48, 64), seed=17)
+        sc.means[:, 2] = 4.0
+        sc.extrinsics[:] = torch.eye(4)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=30.0, bg=(0.0, 0.0, 0.0))
     if name == "c2":               # BASELINE config 2: 131072 Gaussians, 4 views, 256x256, colour+depth
         sc = make_scene()
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))

@@ -11,10 +11,12 @@
 //      atomic cursor and stores (depth bits << 32 | Gaussian id)
 //   4. tile_sort_gather_kernel: one CTA per tile sorts its segment by that 64-bit word in SHARED
 //      MEMORY (the word is unique, so the result equals the stable sort by depth of the
-//      Gaussian-ordered list: 4-pass LSD radix sort on the depth half + a fix-up of equal-depth runs)
-//      and writes keys, values and the gathered 48-B records in sorted order; tiles above
-//      kSmallTileCap go to a second launch (bitonic network in a 128-KB buffer), tiles above
-//      kBigTileCap are sorted in place in global memory by one CTA.
+//      Gaussian-ordered list): a one-pass distribution sort over 4096 depth buckets, with a stable
+//      8-bit LSD radix sort over the id and depth digits as the fallback for clustered / equal depths;
+//      writes keys and values in sorted order; tiles above kSmallTileCap go to a second launch
+//      (bitonic network in a 128-KB buffer), tiles above kBigTileCap are sorted in place in global
+//      memory by one CTA.
+//   5. gather_records_kernel: the 48-B per-Gaussian records copied into sorted order.
 //
 // Why: at C2 (1.6 M pairs, 42 key bits) six LSD passes were latency-bound at ~26 us each plus a
 // 38-us scan/emit and a 38-us range/gather pass (272 us before render); each pair now crosses HBM
@@ -269,10 +271,8 @@ __global__ void __launch_bounds__(256) gather_records_kernel(Workspace ws, int G
   }
 }
 
-// Small tiles (n <= kSmallTileCap): CTA-wide LSD radix sort of the words by their DEPTH half (4 passes
-// of 8 bits, in place in shared memory: a pass holds its words in registers between the load and the
-// scatter), then runs of equal depth - rare, short - are put in Gaussian order.  ~6x fewer
-// instructions than the bitonic network at n ~ 1600 (measured 70 M warp instructions per launch).
+// Fallback of the small-tile sort: CTA-wide stable LSD radix sort of the words (8-bit digits, in place in shared
+// memory: a pass holds its words in registers between the load and the scatter).
 constexpr int kTileSortThreads = 512;
 constexpr int kTileSortWarps = kTileSortThreads / 32;
 
@@ -288,7 +288,6 @@ struct TileSortSmem {
   unsigned int bucket[kDepthBuckets + 1];        // counts -> exclusive bases (bucket[kDepthBuckets] = n)
   unsigned int dexcl[kRadix];                  // exclusive offset of each digit in the CTA
   unsigned int wscan[kTileSortWarps];
-  unsigned int nruns;
   unsigned int dmin, dmax, maxfill;
 };
 
@@ -371,12 +370,14 @@ __device__ __forceinline__ bool distribution_sort_tile(TileSortSmem& s, int n, i
 }
 
 template <int KPT>
-__device__ __forceinline__ void radix_sort_tile_by_depth(TileSortSmem& s, int n, int tid) {
+__device__ __forceinline__ void radix_sort_tile_by_depth(TileSortSmem& s, int n, int tid, int id_passes) {
   const int lane = tid & 31, warp = tid >> 5;
   const int wbase = warp * (32 * KPT);
+  // stable LSD over the whole word: the Gaussian-id digits first (id_passes = ceil(bits(G) / 8)), then the four depth
+  // digits - equal depths come out in Gaussian order with no fix-up, whatever the emission order was
 #pragma unroll 1
-  for (int pass = 0; pass < 4; pass++) {
-    const int shift = 32 + 8 * pass;
+  for (int pass = 0; pass < id_passes + 4; pass++) {
+    const int shift = pass < id_passes ? 8 * pass : 32 + 8 * (pass - id_passes);
     for (int i = tid; i < kTileSortWarps * kRadix; i += kTileSortThreads) (&s.whist[0][0])[i] = 0u;
     unsigned long long w[KPT];
 #pragma unroll
@@ -456,7 +457,7 @@ __global__ void __launch_bounds__(kTileSortThreads, 2) tile_sort_gather_kernel(W
   if (n == 0 || n > kSmallTileCap) return;
   const int tid = threadIdx.x;
   for (int i = tid; i < n; i += kTileSortThreads) s.words[i] = pairs[r.x + i];
-  if (tid == 0) { s.nruns = 0; s.dmin = 0xffffffffu; s.dmax = 0u; s.maxfill = 0u; }
+  if (tid == 0) { s.dmin = 0xffffffffu; s.dmax = 0u; s.maxfill = 0u; }
   __syncthreads();
 #if defined(TSPLAT_EXP_RADIX_ONLY)
   const bool sorted = false;
@@ -465,32 +466,13 @@ __global__ void __launch_bounds__(kTileSortThreads, 2) tile_sort_gather_kernel(W
 #else
   const bool sorted = distribution_sort_tile(s, n, tid);
 #endif
-  if (!sorted) {  // clustered / equal depths: 4-pass LSD radix sort on the depth half + fix-up of equal-depth runs
-    if (n <= 1 * kTileSortThreads) radix_sort_tile_by_depth<1>(s, n, tid);
-    else if (n <= 2 * kTileSortThreads) radix_sort_tile_by_depth<2>(s, n, tid);
-    else if (n <= 4 * kTileSortThreads) radix_sort_tile_by_depth<4>(s, n, tid);
-    else radix_sort_tile_by_depth<8>(s, n, tid);
-    // equal depths: the words of a run are still in emission (atomic) order; order them by Gaussian id
-    unsigned int* runs = &s.whist[0][0];  // free now: up to kTileSortWarps*kRadix = 4096 run starts
-    for (int i = tid; i + 1 < n; i += kTileSortThreads) {
-      const unsigned int d = (unsigned int)(s.words[i] >> 32);
-      if ((unsigned int)(s.words[i + 1] >> 32) == d && (i == 0 || (unsigned int)(s.words[i - 1] >> 32) != d))
-        runs[atomicAdd(&s.nruns, 1u)] = (unsigned int)i;
-    }
-    __syncthreads();
-    for (unsigned int k = tid; k < s.nruns; k += kTileSortThreads) {
-      const int b0 = (int)runs[k];
-      const unsigned int d = (unsigned int)(s.words[b0] >> 32);
-      int e = b0 + 1;
-      while (e < n && (unsigned int)(s.words[e] >> 32) == d) e++;
-      for (int i = b0 + 1; i < e; i++) {  // insertion sort of the run (whole words: same high half)
-        const unsigned long long x = s.words[i];
-        int j = i - 1;
-        while (j >= b0 && s.words[j] > x) { s.words[j + 1] = s.words[j]; j--; }
-        s.words[j + 1] = x;
-      }
-    }
-    __syncthreads();
+  if (!sorted) {  // clustered / equal depths: stable 8-bit LSD radix sort over the id digits, then the depth digits
+    int id_passes = 1;
+    while (id_passes < 4 && (G - 1) >> (8 * id_passes)) id_passes++;
+    if (n <= 1 * kTileSortThreads) radix_sort_tile_by_depth<1>(s, n, tid, id_passes);
+    else if (n <= 2 * kTileSortThreads) radix_sort_tile_by_depth<2>(s, n, tid, id_passes);
+    else if (n <= 4 * kTileSortThreads) radix_sort_tile_by_depth<4>(s, n, tid, id_passes);
+    else radix_sort_tile_by_depth<8>(s, n, tid, id_passes);
   }
   write_sorted_tile(ws, s.words, n, r.x, bid, G, keys_out, vals_out, tid, kTileSortThreads);
 }

@@ -18,8 +18,14 @@
 
 namespace tsplat {
 
-constexpr int kStageEntries = 64;  // list entries per ring stage (2 cull rounds of 32)
-constexpr int kStages = 8;         // ring depth: warps of a tile may drift 7 stages (448 entries) apart
+#ifndef TSPLAT_STAGE_ENTRIES
+#define TSPLAT_STAGE_ENTRIES 64
+#endif
+#ifndef TSPLAT_STAGES
+#define TSPLAT_STAGES 8
+#endif
+constexpr int kStageEntries = TSPLAT_STAGE_ENTRIES;  // list entries per ring stage (cull rounds of 32)
+constexpr int kStages = TSPLAT_STAGES;               // ring depth: warps of a tile may drift kStages-1 stages apart
 constexpr int kConsumerWarps = kTilePix / 32;     // 8
 constexpr int kRenderThreads = kTilePix + 32;     // + the producer warp
 
