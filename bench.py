@@ -34,6 +34,7 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--eager", action="store_true", help="launch every step from Python instead of replaying CUDA graphs")
     return ap.parse_args()
 
 
@@ -128,7 +129,7 @@ def run_ours(args):
     numel = float(VIEWS * 3 * HW * HW)
 
     def to_dev(sc):
-        leaf = lambda t: t.to(dev).requires_grad_(True)
+        leaf = lambda t: t.to(dev)
         return dict(means=leaf(sc.means[None]), cov=leaf(sc.covariances[None]), sh=leaf(sc.harmonics[None]),
                     op=leaf(sc.opacities[None]), ext=sc.extrinsics[None].to(dev), intr=sc.intrinsics[None].to(dev),
                     near=sc.near[None].to(dev), far=sc.far[None].to(dev))
@@ -142,9 +143,11 @@ def run_ours(args):
     def step(s):
         # colour loss = LossMse (loss_mse.py:23-31) fused into the render kernels (forward_mse); depth gets a synthetic
         # upstream gradient (loss_depth.py's role)
-        g = Gaussians(s["means"], s["cov"], s["sh"], s["op"])
-        out, loss = decoder.forward_mse(g, s["ext"], s["intr"], s["near"], s["far"], (HW, HW), target, depth_mode="depth")
-        return out, loss, torch.autograd.grad([loss, out.depth], [s["means"], s["cov"], s["sh"], s["op"]], [one, dLd])
+        leaves = [s[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]  # fresh leaves: capture-safe
+        out, loss = decoder.forward_mse(Gaussians(*leaves), s["ext"], s["intr"], s["near"], s["far"], (HW, HW), target,
+                                        depth_mode="depth")
+        grads = torch.autograd.grad([loss, out.depth], leaves, [one, dLd])
+        return out, loss, grads, loss.grad_fn.state if hasattr(loss.grad_fn, "state") else None
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
@@ -156,6 +159,16 @@ def run_ours(args):
     for i in range(max(args.warmup, 3)):
         step(dev_scenes[i % N_SCENES])
     barrier()
+    # one CUDA graph per resident scene (transplat_b200.graphs): a step is then ONE launch.  Eagerly the host needs
+    # 0.3-0.45 ms per step, which starves the GPUs once 8 ranks share the box's 16 vCPUs.
+    run = [(lambda sc=sc: step(sc)) for sc in dev_scenes]
+    if not args.eager:
+        from transplat_b200.graphs import GraphedStep
+        graphed = [GraphedStep(f, warmup=1, device=dev) for f in run]
+        run = [g.replay for g in graphed]
+        for i in range(max(args.warmup, 3)):
+            run[i % N_SCENES]()
+        barrier()
 
     # ---- timed region: device-resident inputs, one CUDA-event pair per step, L2 flushed between steps.
     # No per-stage events in here: recording an event between every two kernels of the chain costs 4 % of the step
@@ -168,10 +181,14 @@ def run_ours(args):
     for i in range(args.steps):
         flush.zero_()
         ev[i][0].record()
-        step(dev_scenes[i % N_SCENES])
+        run[i % N_SCENES]()
         ev[i][1].record()
     barrier()
     t_wall = time.perf_counter() - t_wall
+    if not args.eager:  # the pair list of a replayed step must not have overflowed its captured capacity
+        from transplat_b200.rasterize import read_status_device
+        for gs in graphed:
+            assert read_status_device(gs.outputs[3]).overflow == 0, "pair-list overflow inside a captured step"
     # ---- same K steps again with the library's per-stage events on the launching stream (roofline.stage_ms)
     _lib.profile_enable(True)
     for i in range(args.steps):
@@ -234,7 +251,8 @@ def run_ours(args):
                    "parallelism": f"scene-sharded x{world} (no collective)",
                    "l2": "256 MiB buffer zeroed between timed steps (outside the event pairs); "
                          f"{N_SCENES} scenes cycled",
-                   "api": "DecoderSplattingCUDA.forward_mse(depth_mode='depth') [render + fused MSE colour loss] + torch.autograd.grad"},
+                   "api": "DecoderSplattingCUDA.forward_mse(depth_mode='depth') [render + fused MSE colour loss] + torch.autograd.grad"
+                          + ("" if args.eager else ", captured once per resident scene in a CUDA graph (transplat_b200.graphs) and replayed")},
         "clocks": clocks,
         "e2e": e2e,
         "gpu_launches": args.steps * launches_per_step(VIEWS, T),
@@ -324,6 +342,16 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
 
     pipe = HostPipeline(dev, slots=3)
     steps = max(10, min(args.steps, 100))
+    if not args.eager:
+        # one CUDA graph per device slot (its input slab sits at a fixed address): the kernels of a step are one launch
+        from transplat_b200.graphs import GraphedStep
+        eager_fn, graphs = step_fn, {}
+
+        def step_fn(dv):
+            key = dv["slab"].data_ptr()
+            if key not in graphs:
+                graphs[key] = GraphedStep(lambda: eager_fn(dv), warmup=1, device=dev)
+            return graphs[key].replay()
     for i in range(6):
         pipe.submit(step_fn, host[i % N_SCENES], outs[i % n_out])
     pipe.drain()
@@ -344,7 +372,8 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
     return {"value": round(world * VIEWS / (ms * 1e-3), 2), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
             "d2h_bytes_per_step": int(d2h), "ms_per_step": round(ms, 4), "steps": steps,
             "how": "pinned host slab (Gaussians, cameras, target) -> H2D stream -> kernels -> D2H stream -> pinned host "
-                   "slabs (colour+depth, all four gradients), 3 slots in flight; "
+                   "slabs (colour+depth, all four gradients), 3 slots in flight"
+                   + ("" if args.eager else ", the kernels of a step replayed from one CUDA graph per slot") + "; "
                    f"{N_SCENES} scenes x {h2d >> 20} MiB cycled (> L2), window timed with CUDA events"}
 
 

@@ -418,3 +418,41 @@ def test_golden_fused_mse_loss():
     (3.0 * w * ((out3.color - target) ** 2).mean() + (out3.color * t("w_color")).sum() + (out3.depth[0] * t("w_depth")).sum()).backward()
     for a, b in zip(l2, l3):
         assert _rel(a.grad, b.grad.cpu().numpy()) <= 1e-5
+
+
+def test_cuda_graph_capture_of_a_whole_step():
+    """transplat_b200.graphs.GraphedStep: forward_mse + backward captured once, replayed with new input VALUES at the
+    same addresses; results equal the eager call's."""
+    from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+    from transplat_b200.graphs import GraphedStep
+    from transplat_b200.rasterize import read_status_device
+    from transplat_b200.synthetic import make_scene
+    dec = DecoderSplattingCUDA().cuda()
+    scs = [make_scene(n_ctx=1, h=32, w=32, n_views=2, seed=60 + i, render_hw=(64, 64)) for i in range(2)]
+    dev = lambda t: t[None].cuda()
+    static = [dev(t).clone() for t in (scs[0].means, scs[0].covariances, scs[0].harmonics, scs[0].opacities)]
+    cam = [dev(t) for t in (scs[0].extrinsics, scs[0].intrinsics, scs[0].near, scs[0].far)]
+    target = torch.rand(1, 2, 3, 64, 64, device="cuda")
+    one = torch.ones((), device="cuda")
+
+    def step():
+        # fresh leaves per call: a leaf made earlier on the default stream would pull that stream into the capture
+        leaves = [t.detach().requires_grad_(True) for t in static]
+        out, loss = dec.forward_mse(Gaussians(*leaves), *cam, (64, 64), target, depth_mode="depth")
+        g = torch.autograd.grad([loss, out.depth], leaves, [one, torch.ones_like(out.depth)])
+        return out.color, out.depth, loss, g, loss.grad_fn.state
+
+    want0 = [x.clone() if torch.is_tensor(x) else [y.clone() for y in x] for x in step()[:4]]
+    gs = GraphedStep(step)
+    for k, sc in enumerate(scs):
+        with torch.no_grad():
+            for dst, src in zip(static, (sc.means, sc.covariances, sc.harmonics, sc.opacities)):
+                dst.copy_(dev(src))
+        color, depth, loss, g, state = gs.replay()
+        torch.cuda.synchronize()
+        assert read_status_device(state).overflow == 0
+        want = want0 if k == 0 else [x.clone() if torch.is_tensor(x) else [y.clone() for y in x] for x in step()[:4]]
+        assert float((color - want[0]).abs().max()) <= 1e-6 and float((depth - want[1]).abs().max()) <= 1e-5
+        assert abs(float(loss) - float(want[2])) <= 1e-7
+        for a, b in zip(g, want[3]):
+            assert float((a - b).abs().max()) <= 1e-5 * float(b.abs().max()) + 1e-12

@@ -166,12 +166,21 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
     dev = means.device
     key = (dev.index, N, G, cfg.H, cfg.W)
     check = cfg.check or _CHECK_MODE
-    if _capacity.unchecked:
+    # Under CUDA-graph capture (transplat_b200.graphs) nothing may touch the host: the capacity must already be
+    # calibrated by an eager call of the same shape, no pinned status buffer is allocated and no event is polled;
+    # the caller checks the overflow flag of the replayed work with read_status_device(state).
+    capturing = torch.cuda.is_current_stream_capturing()
+    if capturing:
+        if key not in _capacity.calibrated and not cfg.d_cap:
+            raise RuntimeError("CUDA-graph capture needs a calibrated pair-list capacity: run one eager call of this "
+                               "problem shape first (or pass RenderConfig.d_cap)")
+        check = "graph"
+    elif _capacity.unchecked:
         _capacity.check_unchecked()
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev)
         while True:
-            d_cap = cfg.d_cap or _capacity.get(key, N * max(G, 1))
+            d_cap = cfg.d_cap or (_capacity.cap[key] if capturing else _capacity.get(key, N * max(G, 1)))
             prob = _problem(cfg, means, cov, sh, opacity, cams)
             layout = TsplatLayout()
             _lib.check(L.tsplat_workspace_layout(C.byref(prob), d_cap, C.byref(layout)), "tsplat_workspace_layout")
@@ -198,6 +207,9 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
                 _lib.check(L.tsplat_forward(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
                                             _ptr(depth), _ptr(radii), C.c_void_p(stream.cuda_stream)),
                            "tsplat_forward")
+            if capturing:
+                host = event = None
+                break
             host = torch.empty(16, dtype=torch.uint8, pin_memory=True)
             _lib.check(L.tsplat_status_read(_ptr(ws), C.c_void_p(host.data_ptr()),
                                             C.c_void_p(stream.cuda_stream)), "tsplat_status_read")
@@ -226,16 +238,27 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
 
 
 def read_status(state) -> TsplatStatus:
+    if state.event is None:  # captured in a CUDA graph: read the device copy
+        return read_status_device(state)
     state.event.synchronize()
     return TsplatStatus.from_buffer_copy(state.status_host.numpy().tobytes())
+
+
+def read_status_device(state) -> TsplatStatus:
+    """Blocking read of the status block straight from the workspace (after a graph replay, or for debugging)."""
+    return TsplatStatus.from_buffer_copy(state.workspace[:16].cpu().numpy().tobytes())
 
 
 def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=None):
     L = _lib.lib()
     means, cov, sh, opacity, cams = state.tensors
-    if _capacity.unchecked:
+    if state.event is None or torch.cuda.is_current_stream_capturing():
+        pass  # CUDA-graph capture: the caller checks read_status_device(state) after a replay
+    elif _capacity.unchecked:
         _capacity.check_unchecked()
-    if state.event.query() or (cfg.check or _CHECK_MODE) == "sync":
+    if state.event is None or torch.cuda.is_current_stream_capturing():
+        pass
+    elif state.event.query() or (cfg.check or _CHECK_MODE) == "sync":
         st = read_status(state)
         if st.overflow:
             raise OverflowError_(
