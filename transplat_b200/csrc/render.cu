@@ -439,9 +439,13 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   const float T_final = inside ? ws.final_T[n * P + pix] : 0.0f;
   float T = T_final;
   const int last_contributor = inside ? (int)ws.n_contrib[n * P + pix] : 0;
-  float accum_rec[CH], last_color[CH], dL_dpix[CH];
+  // The reference keeps accum_rec[ch] (colour behind the current entry) per channel and forms
+  // dL/dalpha = sum_ch (c[ch] - accum_rec[ch]) dL_dpix[ch]; dL_dpix is constant along the list, so the recurrence
+  // runs on the SCALAR accum_dl = sum_ch accum_rec[ch] dL_dpix[ch] (same arithmetic up to summation order).
+  float dL_dpix[CH];
+  float accum_dl = 0.0f, last_cdl = 0.0f;
 #pragma unroll
-  for (int ch = 0; ch < CH; ch++) { accum_rec[ch] = 0.0f; last_color[ch] = 0.0f; dL_dpix[ch] = 0.0f; }
+  for (int ch = 0; ch < CH; ch++) dL_dpix[ch] = 0.0f;
   if (inside) {
     if (dL_dcolor != nullptr) {
 #pragma unroll
@@ -506,16 +510,15 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
             const float inv1ma = __fdividef(1.0f, 1.0f - alpha);
             T = T * inv1ma;
             const float dchannel_dcolor = alpha * T;
-            float dL_dalpha = 0.0f;
+            float cdl = 0.0f;
 #pragma unroll
             for (int ch = 0; ch < CH; ch++) {
-              const float c = col[ch];
-              accum_rec[ch] = last_alpha * last_color[ch] + (1.0f - last_alpha) * accum_rec[ch];
-              last_color[ch] = c;
-              dL_dalpha += (c - accum_rec[ch]) * dL_dpix[ch];
+              cdl += col[ch] * dL_dpix[ch];
               v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
             }
-            dL_dalpha *= T;
+            accum_dl = last_alpha * last_cdl + (1.0f - last_alpha) * accum_dl;
+            last_cdl = cdl;
+            float dL_dalpha = (cdl - accum_dl) * T;
             last_alpha = alpha;
             dL_dalpha += bgT * inv1ma;
             const float dL_dG = a1.y * dL_dalpha;
