@@ -26,8 +26,14 @@ namespace tsplat {
 #endif
 constexpr int kStageEntries = TSPLAT_STAGE_ENTRIES;  // list entries per ring stage (cull rounds of 32)
 constexpr int kStages = TSPLAT_STAGES;               // ring depth: warps of a tile may drift kStages-1 stages apart
-constexpr int kConsumerWarps = kTilePix / 32;     // 8
-constexpr int kRenderThreads = kTilePix + 32;     // + the producer warp
+// A tile's 8 pixel blocks (one warp each) can be split over kSplit CTAs that stream the same list: smaller work
+// items for the tail of the launch at the price of one more producer warp per part
+#ifndef TSPLAT_TILE_SPLIT
+#define TSPLAT_TILE_SPLIT 1
+#endif
+constexpr int kSplit = TSPLAT_TILE_SPLIT;
+constexpr int kConsumerWarps = kTilePix / 32 / kSplit;        // 8 (or 4)
+constexpr int kRenderThreads = kConsumerWarps * 32 + 32;      // + the producer warp
 
 struct RingSmem {
   float4 r0[kStages][kStageEntries];  // x, y, conic.x, conic.y
@@ -61,8 +67,8 @@ __device__ __forceinline__ void issue_stage(Smem& s, int stage, const Workspace&
 // Pixel <-> thread mapping: warp w owns an 8x4 pixel block of the 16x16 tile (2 block columns x 4
 // block rows), lane l the pixel (l & 7, l >> 3) of it.  A compact block makes the per-warp culling
 // effective (the mapping itself is invisible in the results).
-__device__ __forceinline__ void pixel_of_thread(int tid, int& bx, int& by, int& lx, int& ly) {
-  const int warp = tid >> 5, lane = tid & 31;
+__device__ __forceinline__ void pixel_of_thread(int tid, int part, int& bx, int& by, int& lx, int& ly) {
+  const int warp = part * kConsumerWarps + (tid >> 5), lane = tid & 31;
   bx = (warp & 1) * 8; by = (warp >> 1) * 4;
   lx = lane & 7; ly = lane >> 3;
 }
@@ -106,7 +112,8 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
                                                                         float* __restrict__ loss_sum, float loss_scale) {
   __shared__ __align__(128) RingSmem s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int bid = ws.use_order ? (int)ws.tile_order[blockIdx.x] : (int)blockIdx.x;  // longest lists first
+  const int slot = (int)blockIdx.x / kSplit, part = (int)blockIdx.x % kSplit;
+  const int bid = ws.use_order ? (int)ws.tile_order[slot] : slot;  // longest lists first
   const int n = bid / ws.T, tile = bid - n * ws.T;
   const uint2 range = ws.ranges[bid];
   const int total = (int)(range.y - range.x);
@@ -144,7 +151,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
   // ---------------- consumers ----------------
   const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
   int bx, by, lx, ly;
-  pixel_of_thread(tid, bx, by, lx, ly);
+  pixel_of_thread(tid, part, bx, by, lx, ly);
   const int px = tx * kTile + bx + lx, py = ty * kTile + by + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
@@ -241,14 +248,14 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
     if (lane == 0) s.red[warp] = sq;
-    asm volatile("bar.sync 1, %0;" ::"r"(kTilePix) : "memory");  // the 8 consumer warps (the producer has left)
+    asm volatile("bar.sync 1, %0;" ::"r"(kConsumerWarps * 32) : "memory");  // the consumer warps (the producer has left)
     if (warp == 0) {
       unsigned int last = 0;
       if (lane == 0) {
         float t = 0.0f;
 #pragma unroll
         for (int i = 0; i < kConsumerWarps; i++) t += s.red[i];
-        ws.loss_partial[bid] = t;
+        ws.loss_partial[blockIdx.x] = t;
         __threadfence();
         last = atomicAdd(&ws.ctl->loss_done, 1u) == gridDim.x - 1 ? 1u : 0u;
       }
@@ -386,7 +393,8 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   extern __shared__ __align__(128) unsigned char bsmem_raw[];
   RingBwdSmem& s = *reinterpret_cast<RingBwdSmem*>(bsmem_raw);
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int bid = ws.use_order ? (int)ws.tile_order[blockIdx.x] : (int)blockIdx.x;  // longest lists first
+  const int slot = (int)blockIdx.x / kSplit, part = (int)blockIdx.x % kSplit;
+  const int bid = ws.use_order ? (int)ws.tile_order[slot] : slot;  // longest lists first
   const int n = bid / ws.T, tile = bid - n * ws.T;
   const uint2 range = ws.ranges[bid];
   const int total = (int)(range.y - range.x);
@@ -428,7 +436,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   // ---------------- consumers ----------------
   const int tx = tile % ws.tiles_x, ty = tile / ws.tiles_x;
   int bx, by, lx, ly;
-  pixel_of_thread(tid, bx, by, lx, ly);
+  pixel_of_thread(tid, part, bx, by, lx, ly);
   const int px = tx * kTile + bx + lx, py = ty * kTile + by + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
@@ -552,7 +560,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
 
 cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color, float* out_depth,
                                   const TsplatMse* mse, cudaStream_t st) {
-  const int grid = ws.N * ws.T;
+  const int grid = ws.N * ws.T * kSplit;
   if (grid == 0) return cudaSuccess;
   const float* target = mse ? mse->target : nullptr;
   float* loss_sum = mse ? mse->loss_sum : nullptr;
@@ -566,7 +574,7 @@ cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, f
 
 cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,
                                    const float* dL_ddepth, const TsplatMse* mse_in, cudaStream_t st) {
-  const int grid = ws.N * ws.T;
+  const int grid = ws.N * ws.T * kSplit;
   if (grid == 0) return cudaSuccess;
   TsplatMse mse{};
   if (mse_in) mse = *mse_in;
