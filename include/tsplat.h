@@ -63,6 +63,10 @@ extern "C" {
                                          (view*T + tile | depth) key instead of the default bucket path (count per
                                          tile -> scan -> emit -> per-tile sort in shared memory).  Same results. */
 
+#define TSPLAT_FLAG_DEBUG 4           /* the reference's debug=True (GaussianRasterizationSettings.debug, cuda_splatting.py:120):
+                                         synchronise the stream after every stage and report the first failing
+                                         one (TSPLAT_ECUDA + tsplat_last_error names it).  Blocks the host. */
+
 /* fused depth channel (render_depth_cuda, cuda_splatting.py:375-417) */
 #define TSPLAT_DEPTH_NONE 0
 #define TSPLAT_DEPTH_DEPTH 1

@@ -112,3 +112,20 @@ def test_host_camera_prep_plus_oracle_reproduces_reference_host_code():
         ref_op = z["g_op"] + z[f"depth_{mode}_g_op"]
         for a, r in ((acc.means, ref_means), (acc.cov, ref_cov), (acc.opacity, ref_op), (acc.sh, z["g_sh"])):
             assert np.abs(a - r).max() <= 1e-4 * np.abs(r).max()  # tolerance: 1e-4 relative
+
+
+def test_ply_export_matches_reference_table(tmp_path):
+    """transplat_b200.ply_export.export_ply against the vertex table of the UNMODIFIED reference export_ply
+    (tests/golden/ref_ply_small.npz, tests/golden/make_golden_ply.py): same attributes, same float32 rows."""
+    import numpy as np
+    import torch
+    from transplat_b200.ply_export import export_ply, read_ply_table
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_ply_small.npz"))
+    t = lambda k: torch.from_numpy(z[k])
+    path = tmp_path / "sub" / "g.ply"
+    export_ply(t("extrinsics"), t("means"), t("scales"), t("rotations"), t("harmonics"), t("opacities"), path)
+    names, table = read_ply_table(path)
+    assert names == [str(n) for n in z["names"]]
+    assert table.shape == z["table"].shape
+    # quaternions are sign-ambiguous only through scipy's canonicalisation, which both sides share
+    assert np.abs(table - z["table"]).max() <= 1e-5 * np.abs(z["table"]).max()

@@ -456,3 +456,22 @@ def test_cuda_graph_capture_of_a_whole_step():
         assert abs(float(loss) - float(want[2])) <= 1e-7
         for a, b in zip(g, want[3]):
             assert float((a - b).abs().max()) <= 1e-5 * float(b.abs().max()) + 1e-12
+
+
+def test_debug_flag_level1():
+    """GaussianRasterizationSettings.debug=True (cuda_splatting.py:120): every stage is followed by a stream
+    synchronisation and an error check (TSPLAT_FLAG_DEBUG); results are unchanged."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    means, cov, sh, op, cams, cfg = case("tiny_l1")
+    cam = cams[0].cuda()
+    outs = []
+    for debug in (False, True):
+        s = GaussianRasterizationSettings(cfg.H, cfg.W, float(cam[35]), float(cam[36]), cam[37:40], 1.0, cam[0:16].reshape(4, 4),
+                                          cam[16:32].reshape(4, 4), cfg.sh_degree, cam[32:35], False, debug)
+        m = (means[0] * float(cam[40])).cuda().requires_grad_(True)
+        img, radii = GaussianRasterizer(s)(means3D=m, means2D=torch.zeros_like(m, requires_grad=True), shs=sh[0].cuda(),
+                                           opacities=op[0].cuda()[:, None], cov3D_precomp=(cov[0] * float(cam[41])).cuda())
+        img.sum().backward()
+        outs.append((img.detach(), radii, m.grad))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert float((outs[0][2] - outs[1][2]).abs().max()) <= 1e-5 * float(outs[0][2].abs().max())

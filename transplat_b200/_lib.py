@@ -16,6 +16,7 @@ SH_GM3, SH_G3M = 0, 1
 COV_TRIU6, COV_FULL9 = 0, 1
 FLAG_REZERO_GRAD_ACC = 1
 FLAG_SORT_ONESWEEP = 2
+FLAG_DEBUG = 4
 DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",

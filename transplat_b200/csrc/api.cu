@@ -175,6 +175,12 @@ static int cuda_fail(const char* what, cudaError_t e) {
   return TSPLAT_ECUDA;
 }
 
+// debug=True of the reference: CHECK_CUDA(..., debug) = cudaDeviceSynchronize + throw after every kernel
+static cudaError_t debug_sync(const TsplatProblem* p, cudaStream_t st, cudaError_t e) {
+  if (e != cudaSuccess || !(p->flags & TSPLAT_FLAG_DEBUG)) return e;
+  return cudaStreamSynchronize(st);
+}
+
 static int prepare(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
                    LayoutFull* F, Workspace* ws) {
   int rc = validate(p, d_cap);
@@ -236,25 +242,25 @@ static int forward_impl(const TsplatProblem* p, void* workspace, uint64_t worksp
     ws.bucket = (p->flags & TSPLAT_FLAG_SORT_ONESWEEP) ? 0 : 1;
     {
       StageTimer t(kStPre, st);
-      e = launch_preprocess(*p, ws, out_radii, static_cast<char*>(workspace) + F.zero_begin,
-                            (ws.bucket ? F.zero_mid : F.zero_end) - F.zero_begin, st);
+      e = debug_sync(p, st, launch_preprocess(*p, ws, out_radii, static_cast<char*>(workspace) + F.zero_begin,
+                                              (ws.bucket ? F.zero_mid : F.zero_end) - F.zero_begin, st));
     }
     if (e != cudaSuccess) return cuda_fail("preprocess", e);
     if (ws.bucket) {
-      { StageTimer t(kStBin, st); e = launch_bucket_scan_emit(*p, ws, st); }
+      { StageTimer t(kStBin, st); e = debug_sync(p, st, launch_bucket_scan_emit(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("bucket_scan_emit", e);
-      { StageTimer t(kStSort, st); e = launch_bucket_sort_gather(*p, ws, st); }
+      { StageTimer t(kStSort, st); e = debug_sync(p, st, launch_bucket_sort_gather(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("bucket_sort_gather", e);
     } else {
-      { StageTimer t(kStBin, st); e = launch_bin_emit(*p, ws, st); }
+      { StageTimer t(kStBin, st); e = debug_sync(p, st, launch_bin_emit(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("bin_emit", e);
-      { StageTimer t(kStSort, st); e = launch_sort(*p, ws, st); }
+      { StageTimer t(kStSort, st); e = debug_sync(p, st, launch_sort(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("sort", e);
-      { StageTimer t(kStRanges, st); e = launch_ranges_gather(*p, ws, st); }
+      { StageTimer t(kStRanges, st); e = debug_sync(p, st, launch_ranges_gather(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("ranges_gather", e);
     }
   }
-  { StageTimer t(kStRender, st); e = launch_render_forward(*p, ws, out_color, out_depth, mse, st); }
+  { StageTimer t(kStRender, st); e = debug_sync(p, st, launch_render_forward(*p, ws, out_color, out_depth, mse, st)); }
   if (e != cudaSuccess) return cuda_fail("render_forward", e);
   return TSPLAT_OK;
 }
@@ -291,11 +297,11 @@ static int backward_impl(const TsplatProblem* p, void* workspace, uint64_t works
     e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * (uint64_t)p->B * p->V * p->G, st);
     if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
   }
-  { StageTimer t(kStRenderB, st); e = launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, mse, st); }
+  { StageTimer t(kStRenderB, st); e = debug_sync(p, st, launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, mse, st)); }
   if (e != cudaSuccess) return cuda_fail("render_backward", e);
   {
     StageTimer t(kStPreB, st);
-    e = launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D, st);
+    e = debug_sync(p, st, launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D, st));
   }
   if (e != cudaSuccess) return cuda_fail("preprocess_backward", e);
   return TSPLAT_OK;

@@ -105,6 +105,7 @@ class RenderConfig:
     want_means2d_grad: bool = False
     check: str | None = None   # None -> TSPLAT_CHECK env ("auto" default)
     d_cap: int | None = None
+    debug: bool = False        # reference debug=True: synchronise and check after every stage
     sort: str | None = None    # None -> TSPLAT_SORT env ("bucket" default) | "bucket" | "onesweep"
 
 
@@ -122,7 +123,7 @@ def _problem(cfg: RenderConfig, means, cov, sh, opacity, cams) -> TsplatProblem:
     else:
         p.sh_coeffs = sh.shape[2] if cfg.sh_layout == SH_GM3 else sh.shape[3]
     p.sh_layout, p.cov_layout, p.depth_mode, p.sh_l4 = cfg.sh_layout, cfg.cov_layout, cfg.depth_mode, cfg.sh_l4
-    p.flags = _lib.FLAG_SORT_ONESWEEP if (cfg.sort or _SORT_MODE) == "onesweep" else 0
+    p.flags = (_lib.FLAG_SORT_ONESWEEP if (cfg.sort or _SORT_MODE) == "onesweep" else 0) | (_lib.FLAG_DEBUG if cfg.debug else 0)
     p.means, p.cov, p.sh, p.opacity, p.cams = (means.data_ptr(), cov.data_ptr(), sh.data_ptr(),
                                                opacity.data_ptr(), cams.data_ptr())
     return p

@@ -84,7 +84,8 @@ class GaussianRasterizer(nn.Module):
         cam = pack_camera_from_settings(s.viewmatrix, s.projmatrix, s.campos, _scalar(s.tanfovx),
                                         _scalar(s.tanfovy), s.bg)
         cfg = RenderConfig(H=int(s.image_height), W=int(s.image_width), V=1, sh_degree=int(s.sh_degree),
-                           want_radii=True, want_means2d_grad=means2D is not None and means2D.requires_grad)
+                           want_radii=True, want_means2d_grad=means2D is not None and means2D.requires_grad,
+                           debug=bool(s.debug))
         color, _, radii = rasterize(means3D[None], cov3D_precomp[None], feat[None], opacities.reshape(1, -1),
                                     cam, cfg, means2d=means2D if cfg.want_means2d_grad else None)
         return color[0], radii[0]
