@@ -164,10 +164,16 @@ def run_ours(args):
     run = [(lambda sc=sc: step(sc)) for sc in dev_scenes]
     if not args.eager:
         from transplat_b200.graphs import GraphedStep
-        graphed = [GraphedStep(f, warmup=1, device=dev) for f in run]
-        run = [g.replay for g in graphed]
-        for i in range(max(args.warmup, 3)):
-            run[i % N_SCENES]()
+        try:
+            graphed = [GraphedStep(f, warmup=1, device=dev) for f in run]
+            run = [g.replay for g in graphed]
+            for i in range(max(args.warmup, 3)):
+                run[i % N_SCENES]()
+        except Exception as exc:  # never lose the measurement to a capture problem: fall back to eager launches
+            print(f"[bench] CUDA-graph capture failed ({exc!r}); launching eagerly", file=sys.stderr, flush=True)
+            args.eager = True
+            torch.cuda.synchronize()
+            run = [(lambda sc=sc: step(sc)) for sc in dev_scenes]
         barrier()
 
     # ---- timed region: device-resident inputs, one CUDA-event pair per step, L2 flushed between steps.
@@ -350,8 +356,12 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
         def step_fn(dv):
             key = dv["slab"].data_ptr()
             if key not in graphs:
-                graphs[key] = GraphedStep(lambda: eager_fn(dv), warmup=1, device=dev)
-            return graphs[key].replay()
+                try:
+                    graphs[key] = GraphedStep(lambda: eager_fn(dv), warmup=1, device=dev)
+                except Exception as exc:
+                    print(f"[bench] e2e graph capture failed ({exc!r}); eager", file=sys.stderr, flush=True)
+                    graphs[key] = None
+            return graphs[key].replay() if graphs[key] is not None else eager_fn(dv)
     for i in range(6):
         pipe.submit(step_fn, host[i % N_SCENES], outs[i % n_out])
     pipe.drain()
