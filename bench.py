@@ -266,6 +266,10 @@ def run_ours(args):
                      "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": round(top_bytes), "kernel_ms": round(kern[top], 4),
                      "stage_ms": {k: round(v, 4) for k, v in stages.items()},
+                     "per_stage": {k: {"ms": round(kern[k], 4), "algorithmic_bytes": round(alg[k] * VIEWS),
+                                       "achieved": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9, 1) if kern[k] > 0 else None,
+                                       "frac": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9 / peak, 4) if kern[k] > 0 else None,
+                                       "traffic": load_traffic(k)} for k in alg},
                      "stage_ms_how": "CUDA events around each kernel stage on the launching stream, second pass of the "
                                      "same K steps (the timed pass carries no per-stage events)",
                      "step": {"algorithmic_bytes": round(step_bytes),
