@@ -192,6 +192,8 @@ typedef struct TsplatMse {
   const float* dL_dloss; /* backward: 1 float (device), upstream gradient of the loss VALUE                   */
   float scale;           /* backward: 2 * weight / numel (host)                                               */
   float loss_scale;      /* forward: weight / numel (host), so *loss_sum is the reference's loss value        */
+  float* psnr;           /* forward, optional (NULL = skip): [B*V] per-view PSNR of the clipped images,
+                            compute_psnr of src/evaluation/metrics.py:12-19 as logged by model_wrapper.py:149-153 */
 } TsplatMse;
 int tsplat_forward_mse(const TsplatProblem* p, void* workspace, uint64_t workspace_bytes, uint64_t d_cap,
                        float* out_color, float* out_depth, int32_t* out_radii, const TsplatMse* mse,

@@ -121,6 +121,34 @@ loss.backward()
 out.update(mse_target=target[0], mse_weight=torch.tensor(0.7), mse_loss=loss.detach(), mse_g_means=means_r.grad.sum(0),
            mse_g_cov=cov_r.grad.sum(0), mse_g_sh=sh_r.grad.sum(0), mse_g_op=op_r.grad.sum(0))
 
+
+
+# --- the UNMODIFIED compute_psnr (src/evaluation/metrics.py:11-19) the training step logs next to the loss
+# (model_wrapper.py:149-153); lpips / skimage (other metrics of that file) are absent here and stubbed
+def load_metrics(ref_root="/root/reference"):
+    stubs = {"jaxtyping": {"Float": type("Float", (), {"__class_getitem__": classmethod(lambda cls, item: cls)})},
+             "lpips": {"LPIPS": object}, "skimage": {}, "skimage.metrics": {"structural_similarity": None}}
+    saved = {k: sys.modules.get(k) for k in stubs}
+    try:
+        for k, attrs in stubs.items():
+            m = types.ModuleType(k)
+            for a, v in attrs.items():
+                setattr(m, a, v)
+            sys.modules[k] = m
+        spec = importlib.util.spec_from_file_location("_ref_metrics", f"{ref_root}/src/evaluation/metrics.py")
+        mm = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mm)
+        return mm
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                sys.modules.pop(k, None)
+            else:
+                sys.modules[k] = v
+
+
+out["mse_psnr"] = load_metrics().compute_psnr(target[0], img.detach())
+
 path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "ref_host_variants.npz")
 np.savez_compressed(path, **{k: (v.numpy() if torch.is_tensor(v) else v) for k, v in out.items()})
 print("wrote", path, os.path.getsize(path), "bytes;", "visible", out["stats_visible"].tolist(), "high", out["stats_high"].tolist(),

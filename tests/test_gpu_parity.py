@@ -418,6 +418,14 @@ def test_golden_fused_mse_loss():
     (3.0 * w * ((out3.color - target) ** 2).mean() + (out3.color * t("w_color")).sum() + (out3.depth[0] * t("w_depth")).sum()).backward()
     for a, b in zip(l2, l3):
         assert _rel(a.grad, b.grad.cpu().numpy()) <= 1e-5
+    # per-view PSNR out of the same epilogue against the UNMODIFIED compute_psnr (src/evaluation/metrics.py:11-19)
+    with torch.no_grad():
+        out4, loss4, psnr = dec.forward_mse(Gaussians(*[x.detach() for x in leaves]), *cam, (H, W), target, weight=w,
+                                            with_psnr=True)
+    assert float(loss4) == float(loss) and tuple(psnr.shape) == (target.shape[1],)
+    assert np.abs(psnr.cpu().numpy() - zv["mse_psnr"]).max() <= 1e-4  # dB; fp32 log10 of a 12k-term mean
+    mine = -10 * ((target[0].clip(0, 1) - out4.color[0].clip(0, 1)) ** 2).mean(dim=(1, 2, 3)).log10()
+    assert (psnr - mine).abs().max() <= 1e-4
 
 
 def test_cuda_graph_capture_of_a_whole_step():
@@ -456,6 +464,43 @@ def test_cuda_graph_capture_of_a_whole_step():
         assert abs(float(loss) - float(want[2])) <= 1e-7
         for a, b in zip(g, want[3]):
             assert float((a - b).abs().max()) <= 1e-5 * float(b.abs().max()) + 1e-12
+
+
+def test_workspace_freed_without_cycle_collector():
+    """The per-call workspace (22 GiB at C5) must be released by reference counting when the step's outputs go away -
+    no reference cycle through the autograd node - for the plain and the fused-loss entry points."""
+    import gc
+    from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+    from transplat_b200.synthetic import make_scene
+    dec = DecoderSplattingCUDA().cuda()
+    sc = make_scene(n_ctx=1, h=32, w=32, n_views=2, seed=61, render_hw=(64, 64))
+    dev = lambda t: t[None].cuda()
+    leaves = [dev(t).requires_grad_(True) for t in (sc.means, sc.covariances, sc.harmonics, sc.opacities)]
+    cam = [dev(t) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
+    target = torch.rand(1, 2, 3, 64, 64, device="cuda")
+
+    def fused():
+        out, loss = dec.forward_mse(Gaussians(*leaves), *cam, (64, 64), target, depth_mode="depth")
+        torch.autograd.grad(loss + out.depth.sum(), leaves)
+
+    def plain():
+        out = dec.forward(Gaussians(*leaves), *cam, (64, 64), depth_mode="depth")
+        torch.autograd.grad(((out.color - target) ** 2).mean() + out.depth.sum(), leaves)
+
+    for fn in (fused, plain):
+        for _ in range(3):
+            fn()
+        gc.collect()
+        torch.cuda.synchronize()
+        gc.disable()
+        try:
+            base = torch.cuda.memory_allocated()
+            for _ in range(5):
+                fn()
+            torch.cuda.synchronize()
+            assert torch.cuda.memory_allocated() <= base, fn.__name__
+        finally:
+            gc.enable()
 
 
 def test_debug_flag_level1():

@@ -40,7 +40,7 @@ class TsplatLayout(C.Structure):
 
 class TsplatMse(C.Structure):
     _fields_ = [("target", C.c_void_p), ("loss_sum", C.c_void_p), ("color", C.c_void_p), ("dL_dloss", C.c_void_p),
-                ("scale", C.c_float), ("loss_scale", C.c_float)]
+                ("scale", C.c_float), ("loss_scale", C.c_float), ("psnr", C.c_void_p)]
 
 
 class TsplatStatus(C.Structure):

@@ -99,7 +99,7 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   L.n_contrib = take(4 * N * P);
   // ---- backward ----
   L.grad_acc = take(4ull * kAccFloats * NG);
-  out->loss_partial = take(4ull * N * T * 2);  // one partial per render-forward CTA (a tile may be split over 2)
+  out->loss_partial = take(4ull * N * T * 2 * 2);  // loss and PSNR: one partial each per render-forward CTA (a tile may be split over 2)
   L.total_bytes = off;
   return TSPLAT_OK;
 }

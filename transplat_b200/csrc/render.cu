@@ -42,7 +42,7 @@ struct RingSmem {
   uint64_t full[kStages];
   uint64_t empty[kStages];
   int done_warps;
-  float red[kConsumerWarps];  // fused MSE loss: per-warp partial sums
+  float red[2 * kConsumerWarps];  // fused MSE loss and PSNR: per-warp partial sums
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
                                                                         float* __restrict__ out_color,
                                                                         float* __restrict__ out_depth,
                                                                         const float* __restrict__ target,
-                                                                        float* __restrict__ loss_sum, float loss_scale) {
+                                                                        float* __restrict__ loss_sum, float loss_scale,
+                                                                        float* __restrict__ psnr) {
   __shared__ __align__(128) RingSmem s;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int slot = (int)blockIdx.x / kSplit, part = (int)blockIdx.x % kSplit;
@@ -221,6 +222,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
     if (lane == 0) mbar_arrive(&s.empty[st]);
     if (warp_done && ld_volatile_smem(&s.done_warps) == kConsumerWarps) break;
   }
+  float psq = 0.0f;  // per-view PSNR (metrics.py:12-19): sum over channels of (clip(target) - clip(colour))^2
   float sq = 0.0f;  // fused MSE (loss_mse.py:30): this pixel's sum over channels of (colour - target)^2
   if (inside) {
     const size_t pix = (size_t)py * W + px;
@@ -237,25 +239,35 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
       out_depth[n * P + pix] = __fdiv_rn(__fadd_rn(__fadd_rn(x, x), x), 3.0f);
     }
     if (target != nullptr) {
-      const float d0 = c0 - target[(n * 3 + 0) * P + pix], d1 = c1 - target[(n * 3 + 1) * P + pix],
-                  d2 = c2 - target[(n * 3 + 2) * P + pix];
+      const float t0 = target[(n * 3 + 0) * P + pix], t1 = target[(n * 3 + 1) * P + pix], t2 = target[(n * 3 + 2) * P + pix];
+      const float d0 = c0 - t0, d1 = c1 - t1, d2 = c2 - t2;
       sq = d0 * d0 + d1 * d1 + d2 * d2;
+      if (psnr != nullptr) {  // compute_psnr clips both images to [0,1] first (src/evaluation/metrics.py:16-17)
+        const float e0 = __saturatef(t0) - __saturatef(c0), e1 = __saturatef(t1) - __saturatef(c1),
+                    e2 = __saturatef(t2) - __saturatef(c2);
+        psq = e0 * e0 + e1 * e1 + e2 * e2;
+      }
     }
   }
   if (target != nullptr) {
     // CTA partial in a fixed order; the LAST CTA to finish adds all partials in index order: the loss value does
     // not depend on the order in which the tiles complete
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
-    if (lane == 0) s.red[warp] = sq;
+    for (int o = 16; o > 0; o >>= 1) {
+      sq += __shfl_xor_sync(0xffffffffu, sq, o);
+      psq += __shfl_xor_sync(0xffffffffu, psq, o);
+    }
+    if (lane == 0) { s.red[warp] = sq; s.red[kConsumerWarps + warp] = psq; }
     asm volatile("bar.sync 1, %0;" ::"r"(kConsumerWarps * 32) : "memory");  // the consumer warps (the producer has left)
     if (warp == 0) {
       unsigned int last = 0;
+      float* psnr_partial = ws.loss_partial + (size_t)ws.N * ws.T * kSplit;  // indexed by (view, tile, part)
       if (lane == 0) {
-        float t = 0.0f;
+        float t = 0.0f, u = 0.0f;
 #pragma unroll
-        for (int i = 0; i < kConsumerWarps; i++) t += s.red[i];
+        for (int i = 0; i < kConsumerWarps; i++) { t += s.red[i]; u += s.red[kConsumerWarps + i]; }
         ws.loss_partial[blockIdx.x] = t;
+        if (psnr != nullptr) psnr_partial[bid * kSplit + part] = u;
         __threadfence();
         last = atomicAdd(&ws.ctl->loss_done, 1u) == gridDim.x - 1 ? 1u : 0u;
       }
@@ -267,6 +279,17 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
         if (lane == 0) *loss_sum = t * loss_scale;
+        if (psnr != nullptr) {
+          const int per_view = ws.T * kSplit;
+          for (int v = 0; v < ws.N; v++) {
+            float u = 0.0f;
+            for (int i = lane; i < per_view; i += 32) u += __ldcg(psnr_partial + (size_t)v * per_view + i);
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) u += __shfl_xor_sync(0xffffffffu, u, o);
+            // -10 log10(mean over c,h,w); a perfect match gives +inf as in the reference
+            if (lane == 0) psnr[v] = -10.0f * log10f(u / (3.0f * (float)H * (float)W));
+          }
+        }
       }
     }
   }
@@ -565,10 +588,11 @@ cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, f
   const float* target = mse ? mse->target : nullptr;
   float* loss_sum = mse ? mse->loss_sum : nullptr;
   const float loss_scale = mse ? mse->loss_scale : 0.0f;
+  float* psnr = mse ? mse->psnr : nullptr;
   if (p.depth_mode != TSPLAT_DEPTH_NONE)
-    render_forward_kernel<4><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth, target, loss_sum, loss_scale);
+    render_forward_kernel<4><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth, target, loss_sum, loss_scale, psnr);
   else
-    render_forward_kernel<3><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth, target, loss_sum, loss_scale);
+    render_forward_kernel<3><<<grid, kRenderThreads, 0, st>>>(ws, p.H, p.W, p.cams, out_color, out_depth, target, loss_sum, loss_scale, psnr);
   return cudaGetLastError();
 }
 

@@ -62,7 +62,7 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
                  image_shape: tuple, background_color: Tensor, depth_mode: Optional[str] = None,
                  scale_invariant: bool = True, want_radii: bool = False, check: Optional[str] = None,
                  use_sh: bool = True, cams: Optional[Tensor] = None, mse_target: Optional[Tensor] = None,
-                 mse_weight: float = 1.0):
+                 mse_weight: float = 1.0, with_psnr: bool = False):
     """The batched entry point.  With ``mse_target`` [b,v,3,h,w] a fourth value is returned: the reference's MSE colour
     loss ``mse_weight * ((color - target) ** 2).mean()`` (loss_mse.py:23-31), computed inside the render kernels.
   extrinsics [b,v,4,4], intrinsics [b,v,3,3], near/far [b,v],
@@ -82,17 +82,19 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
                        depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check)
     # use_sh=False: the single coefficient is the colour itself (colors_precomp = shs[:, 0, :], cuda_splatting.py:130)
     feat = gaussians.harmonics if use_sh else gaussians.harmonics[..., 0]
-    loss = None
+    loss = psnr = None
     if mse_target is not None:
-        color, depth, radii, loss = rasterize_mse(gaussians.means, gaussians.covariances, feat, gaussians.opacities,
-                                                  cams, cfg, mse_target.reshape(b * v, 3, h, w), mse_weight)
+        out = rasterize_mse(gaussians.means, gaussians.covariances, feat, gaussians.opacities, cams, cfg,
+                            mse_target.reshape(b * v, 3, h, w), mse_weight, with_psnr=with_psnr)
+        color, depth, radii, loss = out[:4]
+        psnr = out[4] if with_psnr else None  # [b*v], the batch axis of compute_psnr's "(b v) c h w" input
     else:
         color, depth, radii = rasterize(gaussians.means, gaussians.covariances, feat, gaussians.opacities, cams, cfg)
     color = color.reshape(b, v, 3, h, w)
     depth = depth.reshape(b, v, h, w) if depth is not None else None
     radii = radii.reshape(b, v, -1) if radii is not None else None
     if mse_target is not None:
-        return color, depth, radii, loss
+        return (color, depth, radii, loss, psnr) if with_psnr else (color, depth, radii, loss)
     return color, depth, radii
 
 
@@ -210,14 +212,17 @@ class DecoderSplattingCUDA(nn.Module):
 
     def forward_mse(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
                     image_shape: tuple, target_image: Tensor, depth_mode: Optional[DepthRenderingMode] = None,
-                    weight: float = 1.0):
+                    weight: float = 1.0, with_psnr: bool = False):
         """forward() + LossMse (src/loss/loss_mse.py:23-31: ``weight * ((prediction.color - batch["target"]["image"])
         ** 2).mean()``) fused into the render kernels: returns (DecoderOutput, loss).  Backpropagating the loss never
-        materialises the colour difference or its gradient."""
-        color, depth, _, loss = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
-                                             self.background_color, depth_mode, mse_target=target_image,
-                                             mse_weight=weight)
-        return DecoderOutput(color, depth), loss
+        materialises the colour difference or its gradient.  ``with_psnr`` adds a third value: the
+        per-view ``compute_psnr`` [b*v] the training step logs as train/psnr_probabilistic (model_wrapper.py:149-153,
+        src/evaluation/metrics.py:12-19), reduced in the same epilogue."""
+        out = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape, self.background_color,
+                           depth_mode, mse_target=target_image, mse_weight=weight, with_psnr=with_psnr)
+        if with_psnr:
+            return DecoderOutput(out[0], out[1]), out[3], out[4]
+        return DecoderOutput(out[0], out[1]), out[3]
 
     def render_depth(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
                      image_shape: tuple, mode: DepthRenderingMode = "depth") -> Tensor:

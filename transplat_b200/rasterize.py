@@ -41,6 +41,7 @@ class _Capacity:
         self.pending = {}
         self.calibrated = set()  # keys whose pair count has been observed at least once
         self.unchecked = []  # (host, event, d_cap) of backward calls launched before their status arrived
+        self.last_num_rendered = None  # pair count of the most recent call whose status has been read
 
     def check_unchecked(self):
         """Raise for an earlier call whose overflow flag could not be read without stalling."""
@@ -81,6 +82,7 @@ class _Capacity:
     def observe(self, key, num_rendered):
         """Keep the capacity at >= 2x the last observed pair count (never shrinks)."""
         self.calibrated.add(key)
+        self.last_num_rendered = int(num_rendered)
         want = min(int(num_rendered * 2) + 4096, (1 << 30) - 1)
         if want > self.cap.get(key, 0):
             self.cap[key] = want
@@ -155,10 +157,12 @@ def _check_inputs(means, cov, sh, opacity, cams, cfg):
         raise RuntimeError(f"cameras must have shape {(B * cfg.V, 64)}, got {tuple(cams.shape)}")
 
 
-def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=None, mse_weight: float = 1.0):
+def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=None, mse_weight: float = 1.0,
+                mse_psnr: bool = False):
     """Launch the forward pipeline; returns (color, depth|None, radii|None, state).  With ``mse_target`` [N,3,H,W] the
     render kernel's epilogue also accumulates the reference's MSE loss (loss_mse.py:23-31); it is returned as
-    ``state.mse[3]`` (a 1-element device tensor) and consumed by backward_raw."""
+    ``state.mse[3]`` (a 1-element device tensor) and consumed by backward_raw; with ``mse_psnr`` the same epilogue also
+    reduces the per-view PSNR of the clipped images (metrics.py:12-19) into ``state.mse[4]`` [N]."""
     L = _lib.lib()
     _check_inputs(means, cov, sh, opacity, cams, cfg)
     means, cov, sh, opacity, cams = (t.contiguous() for t in (means, cov, sh, opacity, cams))
@@ -192,15 +196,16 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
             color = images[:n_col].view(N, 3, cfg.H, cfg.W)
             depth = images[_pad64(n_col):_pad64(n_col) + n_dep].view(N, cfg.H, cfg.W) if cfg.depth_mode else None
             radii = torch.empty((N, G), dtype=torch.int32, device=dev) if cfg.want_radii else None
-            loss = None
+            loss = psnr = None
             if mse_target is not None:
                 if tuple(mse_target.shape) != (N, 3, cfg.H, cfg.W) or mse_target.dtype != torch.float32 or \
                         mse_target.device != dev:
                     raise RuntimeError(f"mse_target must be float32 {(N, 3, cfg.H, cfg.W)} on {dev}")
                 mse_target = mse_target.contiguous()
                 loss = torch.empty(1, dtype=torch.float32, device=dev)
+                psnr = torch.empty(N, dtype=torch.float32, device=dev) if mse_psnr else None
                 m = TsplatMse(target=mse_target.data_ptr(), loss_sum=loss.data_ptr(), color=0, dL_dloss=0, scale=0.0,
-                              loss_scale=mse_weight / float(n_col))
+                              loss_scale=mse_weight / float(n_col), psnr=psnr.data_ptr() if mse_psnr else 0)
                 _lib.check(L.tsplat_forward_mse(C.byref(prob), _ptr(ws), layout.total_bytes, d_cap, _ptr(color),
                                                 _ptr(depth), _ptr(radii), C.byref(m), C.c_void_p(stream.cuda_stream)),
                            "tsplat_forward_mse")
@@ -234,7 +239,10 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
     state.tensors = (means, cov, sh, opacity, cams)
     state.status_host, state.event = host, event
     state.bwd_calls = 0
-    state.mse = (mse_target, color, 2.0 * mse_weight / float(color.numel()), loss) if mse_target is not None else None
+    # color.detach(): the tensor handed to autograd gets grad_fn = the node that owns this state; keeping THAT object here
+    # would close a reference cycle and leave the workspace (22 GiB at C5) to the cycle collector
+    state.mse = ((mse_target, color.detach(), 2.0 * mse_weight / float(color.numel()), loss, psnr)
+                 if mse_target is not None else None)
     return color, depth, radii, state
 
 
@@ -301,10 +309,10 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
             state.problem.flags |= _lib.FLAG_REZERO_GRAD_ACC
         state.bwd_calls += 1
         if fused:
-            target, color, scale, _ = state.mse
+            target, color, scale = state.mse[:3]
             grad_loss = grad_loss.reshape(1).to(torch.float32).contiguous()
             m = TsplatMse(target=target.data_ptr(), loss_sum=0, color=color.data_ptr(), dL_dloss=grad_loss.data_ptr(),
-                          scale=scale, loss_scale=0.0)
+                          scale=scale, loss_scale=0.0, psnr=0)
             _lib.check(L.tsplat_backward_mse(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
                                              state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means),
                                              _ptr(g_cov), _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.byref(m),
@@ -348,32 +356,36 @@ class _RasterizeMse(torch.autograd.Function):
     dL/dloss * 2 w / numel * (colour - target) in the render-backward prologue - no elementwise kernel in between."""
 
     @staticmethod
-    def forward(ctx, means, cov, sh, opacity, cams, cfg, target, weight):
+    def forward(ctx, means, cov, sh, opacity, cams, cfg, target, weight, with_psnr):
         color, depth, radii, state = forward_raw(cfg, means, cov, sh, opacity, cams, mse_target=target,
-                                                 mse_weight=float(weight))
+                                                 mse_weight=float(weight), mse_psnr=bool(with_psnr))
         ctx.cfg, ctx.state = cfg, state
         ctx.set_materialize_grads(False)
         outs = [color, depth if depth is not None else torch.empty(0, device=color.device),
                 radii if radii is not None else torch.empty(0, dtype=torch.int32, device=color.device),
-                state.mse[3].reshape(())]
-        ctx.mark_non_differentiable(outs[2])
+                state.mse[3].reshape(()),
+                state.mse[4] if with_psnr else torch.empty(0, device=color.device)]
+        ctx.mark_non_differentiable(outs[2], outs[4])
         if depth is None:
             ctx.mark_non_differentiable(outs[1])
         return tuple(outs)
 
     @staticmethod
-    def backward(ctx, grad_color, grad_depth, _grad_radii, grad_loss):
+    def backward(ctx, grad_color, grad_depth, _grad_radii, grad_loss, _grad_psnr):
         cfg = ctx.cfg
         g_means, g_cov, g_sh, g_op, _ = backward_raw(cfg, ctx.state, grad_color,
                                                      grad_depth if cfg.depth_mode else None, grad_loss=grad_loss)
-        return g_means, g_cov, g_sh, g_op, None, None, None, None
+        return g_means, g_cov, g_sh, g_op, None, None, None, None, None
 
 
-def rasterize_mse(means, cov, sh, opacity, cams, cfg: RenderConfig, target, weight: float = 1.0):
+def rasterize_mse(means, cov, sh, opacity, cams, cfg: RenderConfig, target, weight: float = 1.0,
+                  with_psnr: bool = False):
     """rasterize() + loss = weight * ((color - target) ** 2).mean() computed inside the render kernels.
-    target [B*V,3,H,W].  Returns color, depth|None, radii|None, loss (0-d tensor)."""
-    color, depth, radii, loss = _RasterizeMse.apply(means, cov, sh, opacity, cams, cfg, target, weight)
-    return color, (depth if cfg.depth_mode else None), (radii if cfg.want_radii else None), loss
+    target [B*V,3,H,W].  Returns color, depth|None, radii|None, loss (0-d tensor) and, with ``with_psnr``, the
+    per-view PSNR [B*V] the reference logs next to the loss (metrics.py:12-19, model_wrapper.py:149-153)."""
+    color, depth, radii, loss, psnr = _RasterizeMse.apply(means, cov, sh, opacity, cams, cfg, target, weight, with_psnr)
+    out = (color, (depth if cfg.depth_mode else None), (radii if cfg.want_radii else None), loss)
+    return out + (psnr,) if with_psnr else out
 
 
 def _pad64(n: int) -> int:
