@@ -127,5 +127,8 @@ def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=Tru
         # accumulators of culled Gaussians (radius 0) are never initialised nor read (preprocess.cu / preprocess_bwd.cu)
         vis = (ins["radii"].cpu().numpy() > 0)[..., None]
         acc_gpu, scr = np.where(vis, acc_gpu, 0.0), np.where(vis, scr[..., :acc_gpu.shape[-1]], 0.0)
+        # the library keeps dL/d(ndc x, y) in slots 0, 1 and applies W/2, H/2 in preprocess_backward
+        acc_gpu[..., 0] *= 0.5 * cfg.W
+        acc_gpu[..., 1] *= 0.5 * cfg.H
         bwd["screen_rel"] = max(rel_err(acc_gpu[..., k], scr[..., k]) for k in range(10 if cfg.depth_mode else 9))
     return fwd, bwd

@@ -98,12 +98,17 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
       const bool vis = cur.radius > 0;
       if (a.dL_dmeans2D) {
         float* d2 = a.dL_dmeans2D + o * 3;
-        d2[0] = vis ? cur.q0.x : 0.0f;
-        d2[1] = vis ? cur.q0.y : 0.0f;
+        d2[0] = vis ? cur.q0.x * (0.5f * (float)p.W) : 0.0f;
+        d2[1] = vis ? cur.q0.y * (0.5f * (float)p.H) : 0.0f;
         d2[2] = 0.0f;
       }
       if (!vis) continue;
-      const float4 q0 = cur.q0, q1 = cur.q1, q2 = cur.q2;
+      const float4 q1 = cur.q1, q2 = cur.q2;
+      float4 q0 = cur.q0;
+      // render_backward accumulates dL/d(ndc x, y) without the pixel scale (one multiply per Gaussian here instead
+      // of one per (pixel, Gaussian) there): d(pixel)/d(ndc) = W/2, H/2
+      q0.x *= 0.5f * (float)p.W;
+      q0.y *= 0.5f * (float)p.H;
       const float dmx = q0.x, dmy = q0.y;
       const float dcon[3] = {q0.z, q0.w, q1.x};
       gop += q1.y;

@@ -54,6 +54,21 @@ __device__ __forceinline__ int ld_volatile_smem(const int* p) {
   return v;
 }
 
+// exp and reciprocal of the hot loops without the denormal guards of __expf / __fdividef (3 and 5 instructions per
+// visit).  ex2.approx.ftz differs from __expf only where the result is denormal (< 1.2e-38): alpha is then below
+// 1/255 either way; forward and backward use the same function, so they classify every (pixel, entry) alike.
+// 1 - alpha lies in [0.01, 1]: rcp.approx.ftz needs no range reduction.
+__device__ __forceinline__ float exp_hot(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x * 1.4426950408889634f));
+  return y;
+}
+__device__ __forceinline__ float rcp_hot(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <class Smem>
 __device__ __forceinline__ void issue_stage(Smem& s, int stage, const Workspace& ws, unsigned int first,
                                             unsigned int cnt) {
@@ -199,7 +214,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
           const float dx = a0.x - pxf, dy = a0.y - pyf;
           const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
           if (done || power > 0.0f) continue;
-          const float alpha = fminf(0.99f, a1.y * __expf(power));
+          const float alpha = fminf(0.99f, a1.y * exp_hot(power));
           if (alpha < 1.0f / 255.0f) continue;
           const float test_T = T * (1.0f - alpha);
           if (test_T < 0.0001f) { done = true; continue; }
@@ -495,7 +510,6 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   const float bg_dot = __ldg(bgp) * dL_dpix[0] + __ldg(bgp + 1) * dL_dpix[1] + __ldg(bgp + 2) * dL_dpix[2];
   const float bgT = -T_final * bg_dot;
   float last_alpha = 0.0f;
-  const float ddelx_dx = 0.5f * (float)W, ddely_dy = 0.5f * (float)H;
   const int my_comp = comp_of_lane(lane);
   const bool my_red = my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9);
   // list positions >= the warp's deepest contributor are never visited by this warp
@@ -528,7 +542,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
           const float4 a1 = r1[j];
           const float dx = a0.x - pxf, dy = a0.y - pyf;
           const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
-          const float Gv = __expf(power);
+          const float Gv = exp_hot(power);
           const float alpha = fminf(0.99f, a1.y * Gv);
           const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
           if (!__any_sync(0xffffffffu, valid)) continue;
@@ -538,7 +552,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
           if (valid) {
             const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
             const float col[4] = {a1.z, a1.w, a2.x, a2.y};
-            const float inv1ma = __fdividef(1.0f, 1.0f - alpha);
+            const float inv1ma = rcp_hot(1.0f - alpha);
             T = T * inv1ma;
             const float dchannel_dcolor = alpha * T;
             float cdl = 0.0f;
@@ -556,8 +570,8 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
             const float gdx = Gv * dx, gdy = Gv * dy;
             const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
             const float dG_ddely = -gdy * a1.x - gdx * a0.w;
-            v[0] = dL_dG * dG_ddelx * ddelx_dx;
-            v[1] = dL_dG * dG_ddely * ddely_dy;
+            v[0] = dL_dG * dG_ddelx;  // x W/2, H/2 applied once per Gaussian in preprocess_backward
+            v[1] = dL_dG * dG_ddely;
             v[2] = -0.5f * gdx * dx * dL_dG;
             v[3] = -0.5f * gdx * dy * dL_dG;
             v[4] = -0.5f * gdy * dy * dL_dG;
