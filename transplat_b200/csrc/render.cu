@@ -69,6 +69,27 @@ __device__ __forceinline__ float rcp_hot(float x) {
   return y;
 }
 
+// shared-memory accesses of the backward's visit loop by 32-bit shared address: through generic pointers the
+// compiler rebuilt the shared window base (S2R SR_CgaCtaId ...) on every visit
+__device__ __forceinline__ float4 lds_f4(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void red_shared_add(uint32_t a, float x) {
+  asm volatile("red.shared.add.f32 [%0], %1;" ::"r"(a), "f"(x) : "memory");
+}
+
 template <class Smem>
 __device__ __forceinline__ void issue_stage(Smem& s, int stage, const Workspace& ws, unsigned int first,
                                             unsigned int cnt) {
@@ -327,6 +348,7 @@ struct RingBwdSmem {
   float acc[kStages][kStageEntries][kAccFloats];
   uint64_t full[kStages];
   uint64_t empty[kStages];
+  unsigned short hitq[kConsumerWarps][kStageEntries];  // per warp: byte offsets (16 j) of the batch's entries that pass the cull
 };
 
 // Reduce v[0..9] over the warp.  On return lane L holds the full sum of component
@@ -514,6 +536,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   const bool my_red = my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9);
   // list positions >= the warp's deepest contributor are never visited by this warp
   const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
+  const unsigned int lt_mask = (1u << lane) - 1u;
 
   for (int b = 0; b < nb; b++) {
     const int st = b % kStages;
@@ -524,70 +547,72 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
     const float4* __restrict__ r2 = s.r2[st];
     const int pos0 = lo - (int)range.x;  // 0-based list position of entry 0 of this batch
     if (pos0 < warp_last) {
-      unsigned int mask[kStageEntries / 32];
+      // survivors of the cull, compacted into this warp's queue (ascending list order): walking a queue costs
+      // 5 instructions per visit, scanning the ballot masks bit by bit cost 15
+      unsigned short* hq = s.hitq[warp];
+      int nhit = 0;
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++) {
         const int j = i * 32 + lane;
-        mask[i] = cull_round(r0, r1, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
+        const unsigned int m = cull_round(r0, r1, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
+        if ((m >> lane) & 1u) hq[nhit + __popc(m & lt_mask)] = (unsigned short)(j * 16);
+        nhit += __popc(m);
       }
+      __syncwarp();
+      uint32_t rb = smem_u32(r0);
+      uint32_t accb = smem_u32(&s.acc[st][0][0]) + (uint32_t)(my_comp * 4);
+      const uint32_t hqb = smem_u32(hq);
+      asm volatile("" : "+r"(rb), "+r"(accb));  // keep them in registers: ptxas otherwise rebuilds both on every visit
+      for (int k = nhit - 1; k >= 0; k--) {
+        const uint32_t off = lds_u16(hqb + 2u * (uint32_t)k);  // 16 j
+        const int pos = pos0 + (int)(off >> 4);
+        const float4 a0 = lds_f4(rb + off);
+        const float4 a1 = lds_f4(rb + off + (uint32_t)sizeof(s.r0));
+        const float dx = a0.x - pxf, dy = a0.y - pyf;
+        const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+        const float Gv = exp_hot(power);
+        const float alpha = fminf(0.99f, a1.y * Gv);
+        const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        if (!__any_sync(0xffffffffu, valid)) continue;
+        // no branch on `valid`: lanes that do not contribute run the same arithmetic with Gv and alpha zeroed, so
+        // every product below is 0 for them; only the four state updates are predicated
+        const float2 a2 = lds_f2(rb + off + 2u * (uint32_t)sizeof(s.r0));
+        const float Gm = valid ? Gv : 0.0f, am = valid ? alpha : 0.0f;
+        const float col[4] = {a1.z, a1.w, a2.x, a2.y};
+        const float inv1ma = rcp_hot(1.0f - alpha);
+        const float Tn = T * inv1ma;
+        const float dchannel_dcolor = am * Tn;
+        float v[10];
+        float cdl = 0.0f;
 #pragma unroll
-      for (int i = kStageEntries / 32 - 1; i >= 0; i--) {
-        unsigned int m = mask[i];
-        while (m) {
-          const int bit = 31 - __clz(m);
-          m ^= 1u << bit;
-          const int j = i * 32 + bit;
-          const int pos = pos0 + j;
-          const float4 a0 = r0[j];
-          const float4 a1 = r1[j];
-          const float dx = a0.x - pxf, dy = a0.y - pyf;
-          const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
-          const float Gv = exp_hot(power);
-          const float alpha = fminf(0.99f, a1.y * Gv);
-          const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-          if (!__any_sync(0xffffffffu, valid)) continue;
-          float v[10];
-#pragma unroll
-          for (int k = 0; k < 10; k++) v[k] = 0.0f;
-          if (valid) {
-            const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
-            const float col[4] = {a1.z, a1.w, a2.x, a2.y};
-            const float inv1ma = rcp_hot(1.0f - alpha);
-            T = T * inv1ma;
-            const float dchannel_dcolor = alpha * T;
-            float cdl = 0.0f;
-#pragma unroll
-            for (int ch = 0; ch < CH; ch++) {
-              cdl += col[ch] * dL_dpix[ch];
-              v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
-            }
-            accum_dl = last_alpha * last_cdl + (1.0f - last_alpha) * accum_dl;
-            last_cdl = cdl;
-            float dL_dalpha = (cdl - accum_dl) * T;
-            last_alpha = alpha;
-            dL_dalpha += bgT * inv1ma;
-            const float dL_dG = a1.y * dL_dalpha;
-            const float gdx = Gv * dx, gdy = Gv * dy;
-            const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
-            const float dG_ddely = -gdy * a1.x - gdx * a0.w;
-            v[0] = dL_dG * dG_ddelx;  // x W/2, H/2 applied once per Gaussian in preprocess_backward
-            v[1] = dL_dG * dG_ddely;
-            v[2] = -0.5f * gdx * dx * dL_dG;
-            v[3] = -0.5f * gdx * dy * dL_dG;
-            v[4] = -0.5f * gdy * dy * dL_dG;
-            v[5] = Gv * dL_dalpha;
-          }
-#ifdef TSPLAT_EXP_NOREDUCE
-          if (v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7] + v[8] + v[9] == 123.456f) s.acc[st][j][0] = 1.0f;
-#else
-          const float r = warp_transpose_reduce10(v, lane);
-#ifdef TSPLAT_EXP_NOATOM
-          if (r == 123.456f) s.acc[st][j][0] = 1.0f;
-#else
-          if (my_red) atomicAdd(&s.acc[st][j][my_comp], r);
-#endif
-#endif
+        for (int ch = 0; ch < CH; ch++) {
+          cdl += col[ch] * dL_dpix[ch];
+          v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
         }
+        if (CH == 3) v[9] = 0.0f;
+        const float acc_new = last_alpha * last_cdl + (1.0f - last_alpha) * accum_dl;
+        const float dL_dalpha = (cdl - acc_new) * Tn + bgT * inv1ma;
+        if (valid) { T = Tn; accum_dl = acc_new; last_cdl = cdl; last_alpha = alpha; }
+        const float dL_dG = a1.y * dL_dalpha;
+        const float gdx = Gm * dx, gdy = Gm * dy;
+        const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
+        const float dG_ddely = -gdy * a1.x - gdx * a0.w;
+        v[0] = dL_dG * dG_ddelx;  // x W/2, H/2 applied once per Gaussian in preprocess_backward
+        v[1] = dL_dG * dG_ddely;
+        v[2] = -0.5f * gdx * dx * dL_dG;
+        v[3] = -0.5f * gdx * dy * dL_dG;
+        v[4] = -0.5f * gdy * dy * dL_dG;
+        v[5] = Gm * dL_dalpha;
+#ifdef TSPLAT_EXP_NOREDUCE
+        if (v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7] + v[8] + v[9] == 123.456f) s.acc[st][0][0] = 1.0f;
+#else
+        const float r = warp_transpose_reduce10(v, lane);
+#ifdef TSPLAT_EXP_NOATOM
+        if (r == 123.456f) s.acc[st][0][0] = 1.0f;
+#else
+        if (my_red) red_shared_add(accb + 3u * off, r);
+#endif
+#endif
       }
     }
     __syncwarp();
