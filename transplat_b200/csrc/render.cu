@@ -43,6 +43,7 @@ struct RingSmem {
   uint64_t empty[kStages];
   int done_warps;
   float red[2 * kConsumerWarps];  // fused MSE loss and PSNR: per-warp partial sums
+  unsigned short hitq[kConsumerWarps][kStageEntries];  // per warp: byte offsets (16 j) of the batch's entries that pass the cull
 };
 
 __device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
@@ -202,6 +203,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
   bool done = !inside;
   bool warp_done = __all_sync(0xffffffffu, done);
   if (warp_done && lane == 0) atomicAdd(&s.done_warps, 1);
+  const unsigned int lt_mask = (1u << lane) - 1u;
 
   for (int b = 0; b < nb; b++) {
     const int st = b % kStages;
@@ -219,35 +221,39 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
       const float4* __restrict__ r0 = s.r0[st];
       const float4* __restrict__ r1 = s.r1[st];
       const float4* __restrict__ r2 = s.r2[st];
-      unsigned int mask[kStageEntries / 32];
-#pragma unroll
-      for (int i = 0; i < kStageEntries / 32; i++)
-        mask[i] = cull_round(r0, r1, r2, i * 32 + lane, i * 32 + lane < cnt, X0, Y0);
-      const unsigned int base = (unsigned int)(b * kStageEntries) + 1u;  // 1-based list position of entry 0
+      // survivors of the cull, compacted into this warp's queue (list order)
+      int nhit = 0;
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++) {
-        unsigned int m = mask[i];
-        while (m) {
-          const int j = i * 32 + (__ffs(m) - 1);
-          m &= m - 1u;
-          const float4 a0 = r0[j];
-          const float4 a1 = r1[j];
-          const float dx = a0.x - pxf, dy = a0.y - pyf;
-          const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
-          if (done || power > 0.0f) continue;
-          const float alpha = fminf(0.99f, a1.y * exp_hot(power));
-          if (alpha < 1.0f / 255.0f) continue;
-          const float test_T = T * (1.0f - alpha);
-          if (test_T < 0.0001f) { done = true; continue; }
-          const float2 a2 = *reinterpret_cast<const float2*>(&r2[j]);
-          const float w = alpha * T;
-          C[0] += a1.z * w;
-          C[1] += a1.w * w;
-          C[2] += a2.x * w;
-          if (CH == 4) C[3] += a2.y * w;
-          T = test_T;
-          last_contributor = base + (unsigned int)j;
-        }
+        const int j = i * 32 + lane;
+        const unsigned int m = cull_round(r0, r1, r2, j, j < cnt, X0, Y0);
+        if ((m >> lane) & 1u) s.hitq[warp][nhit + __popc(m & lt_mask)] = (unsigned short)(j * 16);
+        nhit += __popc(m);
+      }
+      __syncwarp();
+      uint32_t rb = smem_u32(r0);
+      const uint32_t hqb = smem_u32(s.hitq[warp]);
+      asm volatile("" : "+r"(rb));
+      const unsigned int base = (unsigned int)(b * kStageEntries) + 1u;  // 1-based list position of entry 0
+      for (int k = 0; k < nhit; k++) {
+        const uint32_t off = lds_u16(hqb + 2u * (uint32_t)k);  // 16 j
+        const float4 a0 = lds_f4(rb + off);
+        const float4 a1 = lds_f4(rb + off + (uint32_t)sizeof(s.r0));
+        const float dx = a0.x - pxf, dy = a0.y - pyf;
+        const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+        if (done || power > 0.0f) continue;
+        const float alpha = fminf(0.99f, a1.y * exp_hot(power));
+        if (alpha < 1.0f / 255.0f) continue;
+        const float test_T = T * (1.0f - alpha);
+        if (test_T < 0.0001f) { done = true; continue; }
+        const float2 a2 = lds_f2(rb + off + 2u * (uint32_t)sizeof(s.r0));
+        const float w = alpha * T;
+        C[0] += a1.z * w;
+        C[1] += a1.w * w;
+        C[2] += a2.x * w;
+        if (CH == 4) C[3] += a2.y * w;
+        T = test_T;
+        last_contributor = base + (off >> 4);
       }
       if (__all_sync(0xffffffffu, done)) {
         warp_done = true;
