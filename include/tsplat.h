@@ -138,8 +138,9 @@ typedef struct TsplatLayout {
   uint64_t final_T;       /* float  [N, H, W]                                                     */
   uint64_t n_contrib;     /* uint32 [N, H, W]                                                     */
   uint64_t grad_acc;      /* float  [N, G, 12] screen-space gradient accumulators (zeroed by the forward,
-                             filled by the backward): dL/d(ndc x, y) [pixel scale W/2, H/2 not yet applied],
-                             conic xx xy yy, opacity, r g b, depth feature, 2 pad                    */
+                             filled by the backward): moments of u = dL/dG * G over the pixel offsets
+                             (dx, dy, dx^2, dx dy, dy^2) [conic, -1/2 and W/2, H/2 applied by the preprocess
+                             backward], then dL/d opacity, r g b, depth feature, 2 pad               */
   int32_t tiles_x, tiles_y; /* grid                                                               */
   int32_t sort_bits;      /* number of key bits the sort covers                                   */
   int32_t sort_passes;

@@ -127,8 +127,14 @@ def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=Tru
         # accumulators of culled Gaussians (radius 0) are never initialised nor read (preprocess.cu / preprocess_bwd.cu)
         vis = (ins["radii"].cpu().numpy() > 0)[..., None]
         acc_gpu, scr = np.where(vis, acc_gpu, 0.0), np.where(vis, scr[..., :acc_gpu.shape[-1]], 0.0)
-        # the library keeps dL/d(ndc x, y) in slots 0, 1 and applies W/2, H/2 in preprocess_backward
-        acc_gpu[..., 0] *= 0.5 * cfg.W
-        acc_gpu[..., 1] *= 0.5 * cfg.H
+        # slots 0..4 hold the moments S of u = dL/dG * G over (dx, dy, dx^2, dx dy, dy^2); preprocess_backward turns them
+        # into the reference's quantities with the per-Gaussian conic (A, B, C): do the same here
+        con = ins["conic_opacity"].cpu().numpy().astype(np.float64)
+        A, B, Cc = con[..., 0], con[..., 1], con[..., 2]
+        sx, sy = acc_gpu[..., 0].copy(), acc_gpu[..., 1].copy()
+        acc_gpu[..., 0] = -(A * sx + B * sy) * 0.5 * cfg.W
+        acc_gpu[..., 1] = -(Cc * sy + B * sx) * 0.5 * cfg.H
+        acc_gpu[..., 2:5] *= -0.5
+        acc_gpu = np.where(vis, acc_gpu, 0.0)
         bwd["screen_rel"] = max(rel_err(acc_gpu[..., k], scr[..., k]) for k in range(10 if cfg.depth_mode else 9))
     return fwd, bwd

@@ -96,21 +96,14 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
       const ViewIn cur = nxt;
       if (v + 1 < p.V) nxt = fetch(v + 1);
       const bool vis = cur.radius > 0;
-      if (a.dL_dmeans2D) {
-        float* d2 = a.dL_dmeans2D + o * 3;
-        d2[0] = vis ? cur.q0.x * (0.5f * (float)p.W) : 0.0f;
-        d2[1] = vis ? cur.q0.y * (0.5f * (float)p.H) : 0.0f;
-        d2[2] = 0.0f;
+      if (!vis) {
+        if (a.dL_dmeans2D) {
+          float* d2 = a.dL_dmeans2D + o * 3;
+          d2[0] = 0.0f; d2[1] = 0.0f; d2[2] = 0.0f;
+        }
+        continue;
       }
-      if (!vis) continue;
-      const float4 q1 = cur.q1, q2 = cur.q2;
-      float4 q0 = cur.q0;
-      // render_backward accumulates dL/d(ndc x, y) without the pixel scale (one multiply per Gaussian here instead
-      // of one per (pixel, Gaussian) there): d(pixel)/d(ndc) = W/2, H/2
-      q0.x *= 0.5f * (float)p.W;
-      q0.y *= 0.5f * (float)p.H;
-      const float dmx = q0.x, dmy = q0.y;
-      const float dcon[3] = {q0.z, q0.w, q1.x};
+      const float4 q0 = cur.q0, q1 = cur.q1, q2 = cur.q2;
       gop += q1.y;
       float dcol[4] = {q1.z, q1.w, q2.x, q2.y};
       const unsigned char cl = cur.cl;
@@ -128,12 +121,24 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
 
       // ---- cov2D backward (A.4) ----
 #ifdef TSPLAT_EXP_NOCOV
-      if (dmx == 123.456f) continue;
+      if (q0.x == 123.456f) continue;
 #endif
       Cov2D q;
       compute_cov2d(m, fx, fy, tanx, tany, c6, vm, q);
       const float aa = q.a, bb = q.b, cc = q.c;
       const float denom = aa * cc - bb * bb;
+      // render_backward leaves the moments S = sum over pixels of (dL/dG G) (dx, dy, dx^2, dx dy, dy^2) in slots 0..4
+      // (render.cu): with the conic (A, B, C) of the forward (preprocess.cu: c/det, -b/det, a/det)
+      //   dL/dmean2D = -(A S_x + B S_y) W/2, -(C S_y + B S_x) H/2      dL/dconic = -1/2 (S_xx, S_xy, S_yy)
+      const float det_inv = 1.0f / denom;
+      const float cA = cc * det_inv, cB = -bb * det_inv, cC = aa * det_inv;
+      const float dmx = -(cA * q0.x + cB * q0.y) * (0.5f * (float)p.W);
+      const float dmy = -(cC * q0.y + cB * q0.x) * (0.5f * (float)p.H);
+      const float dcon[3] = {-0.5f * q0.z, -0.5f * q0.w, -0.5f * q1.x};
+      if (a.dL_dmeans2D) {
+        float* d2 = a.dL_dmeans2D + o * 3;
+        d2[0] = dmx; d2[1] = dmy; d2[2] = 0.0f;
+      }
       const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
       float dL_da = 0.f, dL_db = 0.f, dL_dc = 0.f;
       float dcov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};

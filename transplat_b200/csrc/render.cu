@@ -599,16 +599,16 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
         const float acc_new = last_alpha * last_cdl + (1.0f - last_alpha) * accum_dl;
         const float dL_dalpha = (cdl - acc_new) * Tn + bgT * inv1ma;
         if (valid) { T = Tn; accum_dl = acc_new; last_cdl = cdl; last_alpha = alpha; }
-        const float dL_dG = a1.y * dL_dalpha;
-        const float gdx = Gm * dx, gdy = Gm * dy;
-        const float dG_ddelx = -gdx * a0.z - gdy * a0.w;
-        const float dG_ddely = -gdy * a1.x - gdx * a0.w;
-        v[0] = dL_dG * dG_ddelx;  // x W/2, H/2 applied once per Gaussian in preprocess_backward
-        v[1] = dL_dG * dG_ddely;
-        v[2] = -0.5f * gdx * dx * dL_dG;
-        v[3] = -0.5f * gdx * dy * dL_dG;
-        v[4] = -0.5f * gdy * dy * dL_dG;
+        // Accumulated per (pixel, entry): the MOMENTS of u = dL/dG * G over the pixel offsets.  Everything that is
+        // constant per (view, Gaussian) - the conic in dL/dmean2D = -(A S_x + B S_y, C S_y + B S_x), the -1/2 of
+        // dL/dconic = -1/2 (S_xx, S_xy, S_yy), the pixel scale W/2, H/2 - is applied once in preprocess_backward.
         v[5] = Gm * dL_dalpha;
+        const float u = a1.y * v[5];
+        v[0] = u * dx;
+        v[1] = u * dy;
+        v[2] = v[0] * dx;
+        v[3] = v[0] * dy;
+        v[4] = v[1] * dy;
 #ifdef TSPLAT_EXP_NOREDUCE
         if (v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7] + v[8] + v[9] == 123.456f) s.acc[st][0][0] = 1.0f;
 #else
