@@ -517,7 +517,7 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   // dL/dalpha = sum_ch (c[ch] - accum_rec[ch]) dL_dpix[ch]; dL_dpix is constant along the list, so the recurrence
   // runs on the SCALAR accum_dl = sum_ch accum_rec[ch] dL_dpix[ch] (same arithmetic up to summation order).
   float dL_dpix[CH];
-  float accum_dl = 0.0f, last_cdl = 0.0f;
+  float accum_dl = 0.0f, w_last = 0.0f, oml_last = 1.0f;
 #pragma unroll
   for (int ch = 0; ch < CH; ch++) dL_dpix[ch] = 0.0f;
   if (inside) {
@@ -537,7 +537,6 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   // bg of the fused depth channel is 0 (render_depth_cuda passes zeros, cuda_splatting.py:410)
   const float bg_dot = __ldg(bgp) * dL_dpix[0] + __ldg(bgp + 1) * dL_dpix[1] + __ldg(bgp + 2) * dL_dpix[2];
   const float bgT = -T_final * bg_dot;
-  float last_alpha = 0.0f;
   const int my_comp = comp_of_lane(lane);
   const bool my_red = my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9);
   // list positions >= the warp's deepest contributor are never visited by this warp
@@ -569,23 +568,25 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
       uint32_t accb = smem_u32(&s.acc[st][0][0]) + (uint32_t)(my_comp * 4);
       const uint32_t hqb = smem_u32(hq);
       asm volatile("" : "+r"(rb), "+r"(accb));  // keep them in registers: ptxas otherwise rebuilds both on every visit
+      const int lim = (last_contributor - pos0) * 16;  // entries at list positions >= last_contributor are skipped
       for (int k = nhit - 1; k >= 0; k--) {
         const uint32_t off = lds_u16(hqb + 2u * (uint32_t)k);  // 16 j
-        const int pos = pos0 + (int)(off >> 4);
         const float4 a0 = lds_f4(rb + off);
         const float4 a1 = lds_f4(rb + off + (uint32_t)sizeof(s.r0));
         const float dx = a0.x - pxf, dy = a0.y - pyf;
         const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
         const float Gv = exp_hot(power);
         const float alpha = fminf(0.99f, a1.y * Gv);
-        const bool valid = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        const bool valid = ((int)off < lim) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, valid)) continue;
-        // no branch on `valid`: lanes that do not contribute run the same arithmetic with Gv and alpha zeroed, so
-        // every product below is 0 for them; only the four state updates are predicated
+        // No branch on `valid`.  A lane that does not contribute runs the same arithmetic with alpha = 0: that leaves
+        // T unchanged (T / (1 - 0)), makes every accumulated product 0, and turns the suffix recurrence into the
+        // identity for the next step (w = 0, 1 - alpha = 1), exactly as if the entry had been skipped.
         const float2 a2 = lds_f2(rb + off + 2u * (uint32_t)sizeof(s.r0));
         const float Gm = valid ? Gv : 0.0f, am = valid ? alpha : 0.0f;
         const float col[4] = {a1.z, a1.w, a2.x, a2.y};
-        const float inv1ma = rcp_hot(1.0f - alpha);
+        const float oma = 1.0f - am;
+        const float inv1ma = rcp_hot(oma);
         const float Tn = T * inv1ma;
         const float dchannel_dcolor = am * Tn;
         float v[10];
@@ -596,9 +597,11 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
           v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
         }
         if (CH == 3) v[9] = 0.0f;
-        const float acc_new = last_alpha * last_cdl + (1.0f - last_alpha) * accum_dl;
+        // accum_dl = last_alpha * last_cdl + (1 - last_alpha) * accum_dl, with w_last = last_alpha * last_cdl and
+        // oml_last = 1 - last_alpha carried as state
+        const float acc_new = w_last + oml_last * accum_dl;
         const float dL_dalpha = (cdl - acc_new) * Tn + bgT * inv1ma;
-        if (valid) { T = Tn; accum_dl = acc_new; last_cdl = cdl; last_alpha = alpha; }
+        T = Tn; accum_dl = acc_new; w_last = am * cdl; oml_last = oma;
         // Accumulated per (pixel, entry): the MOMENTS of u = dL/dG * G over the pixel offsets.  Everything that is
         // constant per (view, Gaussian) - the conic in dL/dmean2D = -(A S_x + B S_y, C S_y + B S_x), the -1/2 of
         // dL/dconic = -1/2 (S_xx, S_xy, S_yy), the pixel scale W/2, H/2 - is applied once in preprocess_backward.
