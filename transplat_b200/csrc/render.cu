@@ -357,66 +357,6 @@ struct RingBwdSmem {
   unsigned short hitq[kConsumerWarps][kStageEntries];  // per warp: byte offsets (16 j) of the batch's entries that pass the cull
 };
 
-// Reduce v[0..9] over the warp.  On return lane L holds the full sum of component
-// comp_of_lane(L) (see below); lanes L and L^1 hold the same component.
-__device__ __forceinline__ float warp_transpose_reduce10(float (&v)[10], int lane) {
-  const unsigned int full = 0xffffffffu;
-  // round 1 (xor 16): 10 -> 5.  upper half-warp keeps 5..9, lower keeps 0..4
-  float a[6];
-  {
-    const bool up = lane & 16;
-#pragma unroll
-    for (int i = 0; i < 5; i++) {
-      const float send = up ? v[i] : v[i + 5];
-      const float keep = up ? v[i + 5] : v[i];
-      a[i] = keep + __shfl_xor_sync(full, send, 16);
-    }
-    a[5] = 0.0f;
-  }
-  // round 2 (xor 8): 6 -> 3
-  float b[4];
-  {
-    const bool up = lane & 8;
-#pragma unroll
-    for (int i = 0; i < 3; i++) {
-      const float send = up ? a[i] : a[i + 3];
-      const float keep = up ? a[i + 3] : a[i];
-      b[i] = keep + __shfl_xor_sync(full, send, 8);
-    }
-    b[3] = 0.0f;
-  }
-  // round 3 (xor 4): 4 -> 2
-  float c[2];
-  {
-    const bool up = lane & 4;
-#pragma unroll
-    for (int i = 0; i < 2; i++) {
-      const float send = up ? b[i] : b[i + 2];
-      const float keep = up ? b[i + 2] : b[i];
-      c[i] = keep + __shfl_xor_sync(full, send, 4);
-    }
-  }
-  // round 4 (xor 2): 2 -> 1
-  float d;
-  {
-    const bool up = lane & 2;
-    const float send = up ? c[0] : c[1];
-    const float keep = up ? c[1] : c[0];
-    d = keep + __shfl_xor_sync(full, send, 2);
-  }
-  d += __shfl_xor_sync(full, d, 1);
-  return d;
-}
-// component index held by `lane` after warp_transpose_reduce10, or -1 (padding slot)
-__device__ __forceinline__ int comp_of_lane(int lane) {
-  const int h16 = (lane >> 4) & 1, h8 = (lane >> 3) & 1, h4 = (lane >> 2) & 1, h2 = (lane >> 1) & 1;
-  const int ib = h2 + 2 * h4;          // slot in b[] (0..3), 3 is padding
-  if (ib == 3) return -1;
-  const int ia = ib + 3 * h8;          // slot in a[] (0..5), 5 is padding
-  if (ia == 5) return -1;
-  return ia + 5 * h16;                 // slot in v[] (0..9)
-}
-
 // one 16-B vector reduction into global memory (sm_90+): 4 fp32 adds, one L2 operation
 __device__ __forceinline__ void red_add_v4(float* addr, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
@@ -537,8 +477,24 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
   // bg of the fused depth channel is 0 (render_depth_cuda passes zeros, cuda_splatting.py:410)
   const float bg_dot = __ldg(bgp) * dL_dpix[0] + __ldg(bgp + 1) * dL_dpix[1] + __ldg(bgp + 2) * dL_dpix[2];
   const float bgT = -T_final * bg_dot;
-  const int my_comp = comp_of_lane(lane);
-  const bool my_red = my_comp >= 0 && !(lane & 1) && (CH == 4 || my_comp != 9);
+  // ---- reduce_plan: which lane ends up with which of the 10 per-entry sums ----
+  // Lane bits b4 b3 b2 pick the component, bits b1 b0 are summed away.  Slots of the accumulator record:
+  //   0 S_x  1 S_y  2 S_xx  3 S_xy  4 S_yy  5 dL/d opacity  6..9 dL/d colour (r, g, b, depth feature).
+  // The swaps of a transposing butterfly cost two selects per exchanged pair; here they are pushed into operands that
+  // are constant along the list: the colour sums are alpha T dL_dpix[c], so each lane multiplies by ITS permutation
+  // of dL_dpix (LAk, LAs, LBk, LBs) and rounds 1 and 2 need no select for them; S_x|S_y and S_xx|S_yy share the
+  // swapped offsets (dk, ds).  S_xy | opacity run as a sixth value through plain sums.  9 selects instead of 22.
+  const bool b4i = lane & 16, b3i = lane & 8;
+  const float dl0 = dL_dpix[0], dl1 = dL_dpix[1], dl2 = dL_dpix[2], dl3 = CH == 4 ? dL_dpix[CH - 1] : 0.0f;
+  float LAk = b3i ? (b4i ? dl3 : dl2) : (b4i ? dl1 : dl0), LAs = b3i ? (b4i ? dl2 : dl3) : (b4i ? dl0 : dl1);
+  float LBk = b3i ? (b4i ? dl1 : dl0) : (b4i ? dl3 : dl2), LBs = b3i ? (b4i ? dl0 : dl1) : (b4i ? dl2 : dl3);
+  const bool g2_writer = (lane & 15) == 1;  // lane 1: S_xy, lane 17: opacity
+  const int my_comp = g2_writer ? (b4i ? 5 : 3)
+                                : ((lane & 4) ? 6 + (b3i ? 2 : 0) + (b4i ? 1 : 0) : (b3i ? (b4i ? 4 : 2) : (b4i ? 1 : 0)));
+  const bool my_red = g2_writer || ((lane & 3) == 0 && (CH == 4 || my_comp != 9));
+  // opaque to ptxas, which would otherwise rebuild the four permuted factors and the lane bits on every visit
+  int lane_bits = lane | (g2_writer ? 32 : 0);
+  asm volatile("" : "+f"(LAk), "+f"(LAs), "+f"(LBk), "+f"(LBs), "+r"(lane_bits));
   // list positions >= the warp's deepest contributor are never visited by this warp
   const int warp_last = __reduce_max_sync(0xffffffffu, last_contributor);
   const unsigned int lt_mask = (1u << lane) - 1u;
@@ -589,14 +545,9 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
         const float inv1ma = rcp_hot(oma);
         const float Tn = T * inv1ma;
         const float dchannel_dcolor = am * Tn;
-        float v[10];
         float cdl = 0.0f;
 #pragma unroll
-        for (int ch = 0; ch < CH; ch++) {
-          cdl += col[ch] * dL_dpix[ch];
-          v[6 + ch] = dchannel_dcolor * dL_dpix[ch];
-        }
-        if (CH == 3) v[9] = 0.0f;
+        for (int ch = 0; ch < CH; ch++) cdl += col[ch] * dL_dpix[ch];
         // accum_dl = last_alpha * last_cdl + (1 - last_alpha) * accum_dl, with w_last = last_alpha * last_cdl and
         // oml_last = 1 - last_alpha carried as state
         const float acc_new = w_last + oml_last * accum_dl;
@@ -605,22 +556,41 @@ __global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspa
         // Accumulated per (pixel, entry): the MOMENTS of u = dL/dG * G over the pixel offsets.  Everything that is
         // constant per (view, Gaussian) - the conic in dL/dmean2D = -(A S_x + B S_y, C S_y + B S_x), the -1/2 of
         // dL/dconic = -1/2 (S_xx, S_xy, S_yy), the pixel scale W/2, H/2 - is applied once in preprocess_backward.
-        v[5] = Gm * dL_dalpha;
-        const float u = a1.y * v[5];
-        v[0] = u * dx;
-        v[1] = u * dy;
-        v[2] = v[0] * dx;
-        v[3] = v[0] * dy;
-        v[4] = v[1] * dy;
-#ifdef TSPLAT_EXP_NOREDUCE
-        if (v[0] + v[1] + v[2] + v[3] + v[4] + v[5] + v[6] + v[7] + v[8] + v[9] == 123.456f) s.acc[st][0][0] = 1.0f;
-#else
-        const float r = warp_transpose_reduce10(v, lane);
+        const float v5 = Gm * dL_dalpha;  // dL/d opacity
+        const float u = a1.y * v5;
+        // ---- transposing warp reduction of the 10 sums (see reduce_plan above the kernel) ----
+        const unsigned int full = 0xffffffffu;
+        const bool b4 = lane_bits & 16, b3 = lane_bits & 8, b2 = lane_bits & 4;
+        const float dk = b4 ? dy : dx, ds = b4 ? dx : dy;
+        const float m1k = u * dk, m1s = u * ds;           // S_x | S_y
+        const float m2k = m1k * dk, m2s = m1s * ds;       // S_xx | S_yy
+        const float v3 = m1k * ds;                        // S_xy
+        const float g2k = b4 ? v5 : v3, g2s = b4 ? v3 : v5;
+        // round 1 (xor 16)
+        float G0 = m1k + __shfl_xor_sync(full, m1s, 16);
+        float G1 = m2k + __shfl_xor_sync(full, m2s, 16);
+        float G2 = g2k + __shfl_xor_sync(full, g2s, 16);
+        float CA = dchannel_dcolor * LAk + __shfl_xor_sync(full, dchannel_dcolor * LAs, 16);
+        float CB = dchannel_dcolor * LBk + __shfl_xor_sync(full, dchannel_dcolor * LBs, 16);
+        // round 2 (xor 8)
+        const float Cx = CA + __shfl_xor_sync(full, CB, 8);
+        const float gk = b3 ? G1 : G0, gs = b3 ? G0 : G1;
+        const float Gx = gk + __shfl_xor_sync(full, gs, 8);
+        G2 += __shfl_xor_sync(full, G2, 8);
+        // round 3 (xor 4)
+        const float mk = b2 ? Cx : Gx, msd = b2 ? Gx : Cx;
+        float Mx = mk + __shfl_xor_sync(full, msd, 4);
+        G2 += __shfl_xor_sync(full, G2, 4);
+        // rounds 4, 5: plain sums
+        Mx += __shfl_xor_sync(full, Mx, 2);
+        G2 += __shfl_xor_sync(full, G2, 2);
+        Mx += __shfl_xor_sync(full, Mx, 1);
+        G2 += __shfl_xor_sync(full, G2, 1);
+        const float r = (lane_bits & 32) ? G2 : Mx;
 #ifdef TSPLAT_EXP_NOATOM
         if (r == 123.456f) s.acc[st][0][0] = 1.0f;
 #else
         if (my_red) red_shared_add(accb + 3u * off, r);
-#endif
 #endif
       }
     }
