@@ -35,6 +35,9 @@ constexpr int kSplit = TSPLAT_TILE_SPLIT;
 constexpr int kConsumerWarps = kTilePix / 32 / kSplit;        // 8 (or 4)
 constexpr int kRenderThreads = kConsumerWarps * 32 + 32;      // + the producer warp
 
+#ifndef TSPLAT_FWD_MIN_BLOCKS
+#define TSPLAT_FWD_MIN_BLOCKS 4  // 54 registers, 4 CTAs per SM: 1 -> 82 registers (0.200 ms), 5 -> 40 (0.166), 7 -> 32 + spills (0.181), 4 -> 0.160
+#endif
 struct RingSmem {
   float4 r0[kStages][kStageEntries];  // x, y, conic.x, conic.y
   float4 r1[kStages][kStageEntries];  // conic.z, opacity, r, g
@@ -141,7 +144,7 @@ __device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0
 // Forward
 // ---------------------------------------------------------------------------------------------
 template <int CH>
-__global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspace ws, int H, int W,
+__global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_forward_kernel(Workspace ws, int H, int W,
                                                                         const TsplatCamera* __restrict__ cams,
                                                                         float* __restrict__ out_color,
                                                                         float* __restrict__ out_depth,
@@ -347,6 +350,9 @@ __global__ void __launch_bounds__(kRenderThreads) render_forward_kernel(Workspac
 // global reductions are one per (tile, Gaussian) instead of one atomic per (pixel, Gaussian,
 // component) as in the reference.
 // ---------------------------------------------------------------------------------------------
+#ifndef TSPLAT_BWD_MIN_BLOCKS
+#define TSPLAT_BWD_MIN_BLOCKS 4  // 4 CTAs per SM by shared memory; 5 or 6 with fewer stages and capped registers are slower
+#endif
 struct RingBwdSmem {
   float4 r0[kStages][kStageEntries];
   float4 r1[kStages][kStageEntries];
@@ -391,7 +397,7 @@ __device__ __forceinline__ void flush_stage(RingBwdSmem& s, int st, int cnt, int
 }
 
 template <int CH>
-__global__ void __launch_bounds__(kRenderThreads) render_backward_kernel(Workspace ws, int H, int W, int G,
+__global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_backward_kernel(Workspace ws, int H, int W, int G,
                                                                          const TsplatCamera* __restrict__ cams,
                                                                          const float* __restrict__ dL_dcolor,
                                                                          const float* __restrict__ dL_ddepth,
