@@ -131,8 +131,10 @@ __device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0
     const float tau = r2[j].w;
     const float a_lo = X0 - a0.x, a_hi = a_lo + 7.0f, b_lo = Y0 - a0.y, b_hi = b_lo + 3.0f;
     const float ax = fminf(fmaxf(0.0f, a_lo), a_hi), by = fminf(fmaxf(0.0f, b_lo), b_hi);
-    const float dy1 = fminf(fmaxf(__fdividef(-a0.w * ax, Cq), b_lo), b_hi);
-    const float dx2 = fminf(fmaxf(__fdividef(-a0.w * by, a0.z), a_lo), a_hi);
+    // raw reciprocals: A, C of a kept Gaussian are normal positive numbers; anything else gives inf/NaN here, which
+    // the clamps turn back into a point of the box, and tau = +inf keeps a degenerate conic anyway
+    const float dy1 = fminf(fmaxf(-a0.w * ax * rcp_hot(Cq), b_lo), b_hi);
+    const float dx2 = fminf(fmaxf(-a0.w * by * rcp_hot(a0.z), a_lo), a_hi);
     const float q1 = 0.5f * (a0.z * ax * ax + Cq * dy1 * dy1) + a0.w * ax * dy1;
     const float q2 = 0.5f * (a0.z * dx2 * dx2 + Cq * by * by) + a0.w * dx2 * by;
     hit = !(fminf(q1, q2) > tau);  // NaN (degenerate conic) => keep
