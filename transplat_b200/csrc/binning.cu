@@ -345,9 +345,14 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
     const unsigned int id = vals[j];
     const size_t o = (size_t)(tile / (unsigned)ws.T) * G + id;
     const float4* __restrict__ gr = ws.grec + o * 3;
-    ws.rec0[j] = gr[0];
-    ws.rec1[j] = gr[1];
-    ws.rec2[j] = gr[2];
+    const float4 g0 = gr[0], g1 = gr[1];
+    float4 g2 = gr[2];
+    // the per-Gaussian cull threshold becomes this pair's block mask (cull.cuh)
+    const unsigned int tl = tile % (unsigned)ws.T, ty = tl / (unsigned)ws.tiles_x, tx = tl - ty * (unsigned)ws.tiles_x;
+    g2.w = __uint_as_float(cull_block_mask(g0, g1.x, g2.w, (float)(tx * kTile), (float)(ty * kTile)));
+    ws.rec0[j] = g0;
+    ws.rec1[j] = g1;
+    ws.rec2[j] = g2;
   }
   if (!ws.use_order) return;
   // The last CTA to finish orders the (view, tile) ids by list length, longest first (counting sort

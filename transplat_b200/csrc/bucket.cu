@@ -259,8 +259,12 @@ __global__ void __launch_bounds__(256) gather_records_kernel(Workspace ws, int G
       const unsigned int j = j0 + u * stride;
       if (j < D) {
         const unsigned int bid = (unsigned int)(keys[j] >> 32);
-        const float4* __restrict__ gr = ws.grec + ((size_t)(bid / (unsigned)ws.T) * G + vals[j]) * 3;
+        const unsigned int view = bid / (unsigned)ws.T, tile = bid - view * (unsigned)ws.T;
+        const float4* __restrict__ gr = ws.grec + ((size_t)view * G + vals[j]) * 3;
         q[u][0] = gr[0]; q[u][1] = gr[1]; q[u][2] = gr[2];
+        // the per-Gaussian cull threshold becomes this pair's block mask (cull.cuh)
+        const unsigned int ty = tile / (unsigned)ws.tiles_x, tx = tile - ty * (unsigned)ws.tiles_x;
+        q[u][2].w = __uint_as_float(cull_block_mask(q[u][0], q[u][1].x, q[u][2].w, (float)(tx * kTile), (float)(ty * kTile)));
       }
     }
 #pragma unroll

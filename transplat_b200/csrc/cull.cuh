@@ -29,4 +29,43 @@ __device__ __forceinline__ float cull_tau(float A, float B, float C, float o) {
   return (tau == tau) ? tau : inf;
 }
 
+// The cull itself, done ONCE per (tile, Gaussian) pair where the sorted records are written (gather kernels): bit w
+// of the result is set iff the entry can pass the alpha test on some pixel of block w of the 16x16 tile at
+// (tileX0, tileY0) - block w = the 8x4 pixels of consumer warp w of the render kernels, columns (w & 1) * 8, rows
+// (w >> 1) * 4.  Exact in the continuous sense: the minimum of
+//   q(dx, dy) = (A dx^2 + C dy^2)/2 + B dx dy      (power = -q)
+// over the rectangle is compared with tau_s.  q is convex with its minimum at the centre, so over a box that does not
+// contain the centre the minimum lies on an edge facing it: with (ax, by) the box point nearest the centre per axis,
+// the candidates are the 1-D minima along dx = ax and along dy = by (if the centre is inside, both are 0).
+// Evaluating q at a slightly different point of the box can only over-estimate the minimum by O(eps^2 q kappa),
+// inside the margin of tau_s.  The render kernels only test their bit (they used to run this test per warp and
+// batch: 160 instructions per 64 entries and warp, a third of the forward's instruction count).
+__device__ __forceinline__ unsigned int cull_block_mask(float4 a0 /* x, y, A, B */, float Cq, float tau, float tileX0,
+                                                        float tileY0) {
+  unsigned int mask = 0;
+  // raw reciprocals: A, C of a kept Gaussian are normal positive numbers; anything else gives inf/NaN, which the
+  // clamps turn back into a point of the box, and tau = +inf keeps a degenerate conic anyway
+  float rA, rC;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rA) : "f"(a0.z));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rC) : "f"(Cq));
+#pragma unroll
+  for (int cx = 0; cx < 2; cx++) {
+    const float a_lo = tileX0 + 8.0f * cx - a0.x, a_hi = a_lo + 7.0f;
+    const float ax = fminf(fmaxf(0.0f, a_lo), a_hi);
+    const float dy1_free = -a0.w * ax * rC;
+    const float q1x = a0.z * ax * ax;
+#pragma unroll
+    for (int ry = 0; ry < 4; ry++) {
+      const float b_lo = tileY0 + 4.0f * ry - a0.y, b_hi = b_lo + 3.0f;
+      const float by = fminf(fmaxf(0.0f, b_lo), b_hi);
+      const float dy1 = fminf(fmaxf(dy1_free, b_lo), b_hi);
+      const float dx2 = fminf(fmaxf(-a0.w * by * rA, a_lo), a_hi);
+      const float q1 = 0.5f * (q1x + Cq * dy1 * dy1) + a0.w * ax * dy1;
+      const float q2 = 0.5f * (a0.z * dx2 * dx2 + Cq * by * by) + a0.w * dx2 * by;
+      if (!(fminf(q1, q2) > tau)) mask |= 1u << (ry * 2 + cx);  // NaN (degenerate conic) => keep
+    }
+  }
+  return mask;
+}
+
 }  // namespace tsplat

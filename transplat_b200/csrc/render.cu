@@ -113,32 +113,13 @@ __device__ __forceinline__ void pixel_of_thread(int tid, int part, int& bx, int&
   lx = lane & 7; ly = lane >> 3;
 }
 
-// Per-warp culling: bit l of the result is set iff entry j (one per lane) can pass the alpha test on some
-// pixel of the warp's block [X0, X0+7] x [Y0, Y0+3].  Exact in the continuous sense: the minimum of
-//   q(dx, dy) = (A dx^2 + C dy^2)/2 + B dx dy      (power = -q)
-// over the rectangle is compared with tau_s (rec2.w, cull_tau in cull.cuh).  q is convex with its
-// minimum at the centre, so over a box that does not contain the centre the minimum lies on an edge
-// facing it: with (ax, by) the box point nearest the centre per axis, the candidates are the 1-D minima
-// along dx = ax and along dy = by (if the centre is inside, both are 0).  Evaluating q at a slightly
-// different point of the box can only over-estimate the minimum by O(eps^2 q kappa), inside the margin.
-__device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r0, const float4* __restrict__ r1,
-                                                   const float4* __restrict__ r2, int j, bool in_range, float X0,
-                                                   float Y0) {
+// Per-warp culling: bit l of the result is set iff entry j (one per lane) can pass the alpha test on some pixel of
+// this warp's 8x4 block.  The test itself (minimum of the conic quadratic over the block against tau_s) is done once
+// per (tile, Gaussian) pair by the gather kernels, which leave one bit per block in rec2.w (cull.cuh:
+// cull_block_mask); here a lane only looks at its warp's bit.
+__device__ __forceinline__ unsigned int cull_round(const float4* __restrict__ r2, int j, bool in_range, int block) {
   bool hit = false;
-  if (in_range) {
-    const float4 a0 = r0[j];     // x, y, A, B
-    const float Cq = r1[j].x;    // C
-    const float tau = r2[j].w;
-    const float a_lo = X0 - a0.x, a_hi = a_lo + 7.0f, b_lo = Y0 - a0.y, b_hi = b_lo + 3.0f;
-    const float ax = fminf(fmaxf(0.0f, a_lo), a_hi), by = fminf(fmaxf(0.0f, b_lo), b_hi);
-    // raw reciprocals: A, C of a kept Gaussian are normal positive numbers; anything else gives inf/NaN here, which
-    // the clamps turn back into a point of the box, and tau = +inf keeps a degenerate conic anyway
-    const float dy1 = fminf(fmaxf(-a0.w * ax * rcp_hot(Cq), b_lo), b_hi);
-    const float dx2 = fminf(fmaxf(-a0.w * by * rcp_hot(a0.z), a_lo), a_hi);
-    const float q1 = 0.5f * (a0.z * ax * ax + Cq * dy1 * dy1) + a0.w * ax * dy1;
-    const float q2 = 0.5f * (a0.z * dx2 * dx2 + Cq * by * by) + a0.w * dx2 * by;
-    hit = !(fminf(q1, q2) > tau);  // NaN (degenerate conic) => keep
-  }
+  if (in_range) hit = (__float_as_uint(r2[j].w) >> block) & 1u;
   return __ballot_sync(0xffffffffu, hit);
 }
 
@@ -198,7 +179,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_
   const int px = tx * kTile + bx + lx, py = ty * kTile + by + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
-  const float X0 = (float)(tx * kTile + bx), Y0 = (float)(ty * kTile + by);
+  const int block = part * kConsumerWarps + warp;  // this warp's bit in the pair's block mask (rec2.w)
 
   float T = 1.0f;
   float C[CH];
@@ -231,7 +212,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++) {
         const int j = i * 32 + lane;
-        const unsigned int m = cull_round(r0, r1, r2, j, j < cnt, X0, Y0);
+        const unsigned int m = cull_round(r2, j, j < cnt, block);
         if ((m >> lane) & 1u) s.hitq[warp][nhit + __popc(m & lt_mask)] = (unsigned short)(j * 16);
         nhit += __popc(m);
       }
@@ -454,7 +435,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
   const int px = tx * kTile + bx + lx, py = ty * kTile + by + ly;
   const bool inside = px < W && py < H;
   const float pxf = (float)px, pyf = (float)py;
-  const float X0 = (float)(tx * kTile + bx), Y0 = (float)(ty * kTile + by);
+  const int block = part * kConsumerWarps + warp;  // this warp's bit in the pair's block mask (rec2.w)
   const size_t P = (size_t)H * W;
   const size_t pix = (size_t)py * W + px;
 
@@ -523,7 +504,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
 #pragma unroll
       for (int i = 0; i < kStageEntries / 32; i++) {
         const int j = i * 32 + lane;
-        const unsigned int m = cull_round(r0, r1, r2, j, j < cnt && pos0 + j < warp_last, X0, Y0);
+        const unsigned int m = cull_round(r2, j, j < cnt && pos0 + j < warp_last, block);
         if ((m >> lane) & 1u) hq[nhit + __popc(m & lt_mask)] = (unsigned short)(j * 16);
         nhit += __popc(m);
       }
