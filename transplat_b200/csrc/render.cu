@@ -513,7 +513,8 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
       uint32_t accb = smem_u32(&s.acc[st][0][0]) + (uint32_t)(my_comp * 4);
       const uint32_t hqb = smem_u32(hq);
       asm volatile("" : "+r"(rb), "+r"(accb));  // keep them in registers: ptxas otherwise rebuilds both on every visit
-      const int lim = (last_contributor - pos0) * 16;  // entries at list positions >= last_contributor are skipped
+      // entries at list positions >= last_contributor are skipped (clamped: no overflow for any list length)
+      const int lim = max(min(last_contributor - pos0, kStageEntries), 0) * 16;
       for (int k = nhit - 1; k >= 0; k--) {
         const uint32_t off = lds_u16(hqb + 2u * (uint32_t)k);  // 16 j
         const float4 a0 = lds_f4(rb + off);
