@@ -269,7 +269,11 @@ def run_ours(args):
                      "per_stage": {k: {"ms": round(kern[k], 4), "algorithmic_bytes": round(alg[k] * VIEWS),
                                        "achieved": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9, 1) if kern[k] > 0 else None,
                                        "frac": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9 / peak, 4) if kern[k] > 0 else None,
-                                       "traffic": load_traffic(k)} for k in alg},
+                                       "traffic": load_traffic(k), **load_issue(k)} for k in alg},
+                     "issue": {"what": "the two render kernels have no dense contraction and move little memory: "
+                                       "they are bound by instruction issue (ncu --set full capture of this command, "
+                                       "profiles/traffic.json: smsp__issue_active, smsp__inst_executed per launch)",
+                               **load_issue(top)},
                      "stage_ms_how": "CUDA events around each kernel stage on the launching stream, second pass of the "
                                      "same K steps (the timed pass carries no per-stage events)",
                      "step": {"algorithmic_bytes": round(step_bytes),
@@ -306,6 +310,15 @@ def load_traffic(kernel: str):
         return d.get(kernel)
     except Exception:
         return None
+
+
+def load_issue(kernel: str) -> dict:
+    """issue-slot utilisation / warp instructions per launch of a render kernel from the committed ncu summary."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        return dict(d.get("_issue", {}).get(kernel, {}))
+    except Exception:
+        return {}
 
 
 def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
