@@ -70,6 +70,7 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   L.ranges = take(8ull * N * T);
   out->tile_count = take(4ull * N * T);
   out->tile_cursor = take(4ull * N * T);
+  out->tile_last = take(4ull * N * T);
   out->zero_mid = off;
   out->scan_state = take(8ull * out->num_scan_tiles);
   out->sort_state = take(4ull * kRadix * out->num_sort_tiles * L.sort_passes);
@@ -130,6 +131,7 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   w.tile_order = reinterpret_cast<unsigned int*>(b + F.tile_order);
   w.tile_count = reinterpret_cast<unsigned int*>(b + F.tile_count);
   w.tile_cursor = reinterpret_cast<unsigned int*>(b + F.tile_cursor);
+  w.tile_last = reinterpret_cast<unsigned int*>(b + F.tile_last);
   w.big_list = reinterpret_cast<unsigned int*>(b + F.big_list);
   w.bucket = 1;
   w.use_order = (uint64_t)N * (uint64_t)(L.tiles_x * L.tiles_y) <= (uint64_t)kOrderMaxTiles ? 1 : 0;

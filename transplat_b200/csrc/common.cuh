@@ -71,6 +71,8 @@ struct Workspace {
   float4* rec2;  // b, depth feature, bits(Gaussian id), cull threshold tau_s (cull.cuh)
   unsigned int* tile_count;        // bucket path: pairs per (view, tile), counted by the preprocess kernel
   unsigned int* tile_cursor;       // bucket path: emission cursors per (view, tile)
+  unsigned int* tile_last;         // per (view, tile): 1 + list position of the deepest contributor of any pixel
+                                   // (render_forward, atomicMax); render_backward starts its walk there
   unsigned int* big_list;          // bucket path: (view, tile) ids with more than kSmallTileCap pairs
   int bucket;                      // 1: bucket path (count -> scan -> emit -> per-tile sort), 0: onesweep LSD path
   unsigned int* tile_order;        // (view, tile) ids, heaviest list first (render launch order)
@@ -85,7 +87,7 @@ struct Workspace {
 
 struct LayoutFull {
   TsplatLayout pub;
-  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, loss_partial, scan_state, sort_state, tile_order, tile_count, tile_cursor, big_list,
+  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, loss_partial, scan_state, sort_state, tile_order, tile_count, tile_cursor, tile_last, big_list,
       zero_begin, zero_mid, zero_end;  // [zero_begin, zero_mid) is all the bucket path needs cleared
   int num_scan_tiles, num_sort_tiles;
 };

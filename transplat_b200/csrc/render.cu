@@ -250,6 +250,10 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_
     if (lane == 0) mbar_arrive(&s.empty[st]);
     if (warp_done && ld_volatile_smem(&s.done_warps) == kConsumerWarps) break;
   }
+  {  // the backward never needs the list behind the tile's deepest contributor (28 % of a C2 list on average)
+    const unsigned int wm = __reduce_max_sync(0xffffffffu, last_contributor);
+    if (lane == 0 && wm) atomicMax(&ws.tile_last[bid], wm);
+  }
   float psq = 0.0f;  // per-view PSNR (metrics.py:12-19): sum over channels of (clip(target) - clip(colour))^2
   float sq = 0.0f;  // fused MSE (loss_mse.py:30): this pixel's sum over channels of (colour - target)^2
   if (inside) {
@@ -391,7 +395,8 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
   const int slot = (int)blockIdx.x / kSplit, part = (int)blockIdx.x % kSplit;
   const int bid = ws.use_order ? (int)ws.tile_order[slot] : slot;  // longest lists first
   const int n = bid / ws.T, tile = bid - n * ws.T;
-  const uint2 range = ws.ranges[bid];
+  uint2 range = ws.ranges[bid];
+  range.y = range.x + min(range.y - range.x, ws.tile_last[bid]);  // nothing contributes behind this position
   const int total = (int)(range.y - range.x);
   const int nb = (total + kStageEntries - 1) / kStageEntries;
 
