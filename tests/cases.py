@@ -26,6 +26,10 @@ def case(name: str):
     if name == "deg2_l1":          # SH degree 2 with 9 coefficients, level 1
         sc = make_scene(n_ctx=1, h=32, w=32, n_views=1, render_hw=(64, 64), seed=8, sh_degree=2)
         return _pack(sc, level=1, B=1, depth_mode=0, cov_mul=4.0, bg=(0.1, 0.1, 0.1))
+    if name in ("deg0_l2", "deg1_l2", "deg3_l2"):  # the SH degrees the flagship config does not use (1, 4, 16 coefficients)
+        deg = int(name[3])
+        sc = make_scene(n_ctx=1, h=40, w=40, n_views=2, render_hw=(56, 72), seed=50 + deg, sh_degree=deg)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=5.0, bg=(0.3, 0.1, 0.6))
     if name == "dense_big":        # few tiles, very long lists: > 4096 and > 16384 pairs per tile (big-tile sort paths)
         sc = make_scene(n_ctx=1, h=144, w=144, n_views=2, render_hw=(32, 48), seed=31)
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=120.0, bg=(0.0, 0.0, 0.0))

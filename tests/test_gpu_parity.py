@@ -45,6 +45,13 @@ def test_stage_by_stage_parity(name, sort):
     _assert_reports(fwd, bwd)
 
 
+@pytest.mark.parametrize("name", ["deg0_l2", "deg1_l2", "deg3_l2"])
+def test_other_sh_degrees(name):
+    """SH degrees 0, 1 and 3 (the flagship config uses 4, deg2_l1 covers 2): forward and backward against the oracle."""
+    fwd, bwd = run_both(*case(name))
+    _assert_reports(fwd, bwd)
+
+
 def test_long_tile_lists_take_the_big_tile_sort_paths():
     """6 tiles per view with 15 000 - 20 000 pairs each: the 128-KB shared-memory sort (<= 16384) and the in-place
     global-memory sort (> 16384)."""
