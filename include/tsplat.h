@@ -66,6 +66,12 @@ extern "C" {
 #define TSPLAT_FLAG_DEBUG 4           /* the reference's debug=True (GaussianRasterizationSettings.debug, cuda_splatting.py:120):
                                          synchronise the stream after every stage and report the first failing
                                          one (TSPLAT_ECUDA + tsplat_last_error names it).  Blocks the host. */
+#define TSPLAT_FLAG_BWD_RENDER_ONLY 8      /* tsplat_backward[_mse]: stop after the render-backward stage (the screen-space
+                                              accumulators are complete; no per-Gaussian gradient is written yet) */
+#define TSPLAT_FLAG_BWD_GAUSSIANS_ONLY 16  /* tsplat_backward[_mse]: only the per-Gaussian stage, for the Gaussians
+                                              [g_begin, g_begin + g_count) - a view-sharded caller reduces the
+                                              gradients of one range over the ranks while the next is computed
+                                              (transplat_b200/parallel.py) */
 
 /* fused depth channel (render_depth_cuda, cuda_splatting.py:375-417) */
 #define TSPLAT_DEPTH_NONE 0
@@ -116,6 +122,8 @@ typedef struct TsplatProblem {
   const float* sh;      /* [B, G, M, 3] / [B, G, 3, M] / colors_precomp [B, G, 3]                */
   const float* opacity; /* [B, G]                                                                */
   const TsplatCamera* cams; /* [B*V]                                                             */
+  int32_t g_begin;    /* tsplat_backward with TSPLAT_FLAG_BWD_GAUSSIANS_ONLY: the Gaussian range      */
+  int32_t g_count;    /* [g_begin, g_begin + g_count) of every scene (g_begin a multiple of 64; 0 = all) */
 } TsplatProblem;
 
 /* Byte offsets of the inspectable workspace sections (all 256-B aligned).  N = B*V views. */

@@ -17,6 +17,8 @@ COV_TRIU6, COV_FULL9 = 0, 1
 FLAG_REZERO_GRAD_ACC = 1
 FLAG_SORT_ONESWEEP = 2
 FLAG_DEBUG = 4
+FLAG_BWD_RENDER_ONLY = 8
+FLAG_BWD_GAUSSIANS_ONLY = 16
 DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
@@ -28,7 +30,8 @@ EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "ts
 class TsplatProblem(C.Structure):
     _fields_ = [(n, C.c_int32) for n in (
         "B", "G", "V", "H", "W", "sh_degree", "sh_coeffs", "sh_layout", "cov_layout", "depth_mode",
-        "sh_l4", "flags")] + [(n, C.c_void_p) for n in ("means", "cov", "sh", "opacity", "cams")]
+        "sh_l4", "flags")] + [(n, C.c_void_p) for n in ("means", "cov", "sh", "opacity", "cams")] + [
+        (n, C.c_int32) for n in ("g_begin", "g_count")]
 
 
 class TsplatLayout(C.Structure):

@@ -294,16 +294,29 @@ static int backward_impl(const TsplatProblem* p, void* workspace, uint64_t works
   cudaError_t e;
   // grad_acc is zero after the forward (its preprocess clears the kept Gaussians' accumulators); a repeated
   // backward over the same forward state asks for a fresh clear
-  if (p->flags & TSPLAT_FLAG_REZERO_GRAD_ACC) {
+  if ((p->flags & TSPLAT_FLAG_REZERO_GRAD_ACC) && !(p->flags & TSPLAT_FLAG_BWD_GAUSSIANS_ONLY)) {
     StageTimer t(kStZeroB, st);
     e = cudaMemsetAsync(ws.grad_acc, 0, sizeof(float) * kAccFloats * (uint64_t)p->B * p->V * p->G, st);
     if (e != cudaSuccess) return cuda_fail("memset(grad_acc)", e);
   }
-  { StageTimer t(kStRenderB, st); e = debug_sync(p, st, launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, mse, st)); }
-  if (e != cudaSuccess) return cuda_fail("render_backward", e);
+  if (!(p->flags & TSPLAT_FLAG_BWD_GAUSSIANS_ONLY)) {
+    StageTimer t(kStRenderB, st);
+    e = debug_sync(p, st, launch_render_backward(*p, ws, dL_dcolor, dL_ddepth, mse, st));
+    if (e != cudaSuccess) return cuda_fail("render_backward", e);
+  }
+  if (p->flags & TSPLAT_FLAG_BWD_RENDER_ONLY) return TSPLAT_OK;
+  int g_begin = 0, g_count = p->G;
+  if ((p->flags & TSPLAT_FLAG_BWD_GAUSSIANS_ONLY) && p->g_count > 0) {
+    g_begin = p->g_begin; g_count = p->g_count;
+    if (g_begin < 0 || g_begin % kPreBwdBlock != 0 || (int64_t)g_begin + g_count > p->G) {
+      set_error("backward: bad Gaussian range [%d, +%d) (G = %d, g_begin must be a multiple of %d)", g_begin, g_count, p->G, kPreBwdBlock);
+      return TSPLAT_EINVAL;
+    }
+  }
   {
     StageTimer t(kStPreB, st);
-    e = debug_sync(p, st, launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D, st));
+    e = debug_sync(p, st, launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D,
+                                                     g_begin, g_count, st));
   }
   if (e != cudaSuccess) return cuda_fail("preprocess_backward", e);
   return TSPLAT_OK;

@@ -14,6 +14,7 @@ namespace tsplat {
 struct PreBwdArgs {
   TsplatProblem p;
   int cov_floats, sh_floats, bulk_ok;
+  int g_begin, g_end;  // Gaussian range of this launch (every scene); g_begin is a multiple of kPreBwdBlock
   float* dL_dmeans;
   float* dL_dcov;
   float* dL_dsh;
@@ -32,8 +33,8 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
   const TsplatProblem& p = a.p;
   const int tid = threadIdx.x;
   const int b = blockIdx.y;
-  const int g0 = blockIdx.x * kPreBwdBlock;
-  const int cnt = min(kPreBwdBlock, p.G - g0);
+  const int g0 = a.g_begin + blockIdx.x * kPreBwdBlock;
+  const int cnt = min(kPreBwdBlock, a.g_end - g0);
   const size_t gbase = (size_t)b * p.G + g0;
   const float* g_mean = p.means + gbase * 3;
   const float* g_cov = p.cov + gbase * a.cov_floats;
@@ -264,9 +265,12 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
 }
 
 cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& ws, float* dL_dmeans, float* dL_dcov,
-                                       float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, cudaStream_t st) {
+                                       float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, int g_begin, int g_count,
+                                       cudaStream_t st) {
+  if (g_count <= 0) return cudaSuccess;
   PreBwdArgs a;
   a.p = p;
+  a.g_begin = g_begin; a.g_end = g_begin + g_count;
   a.cov_floats = p.cov_layout == TSPLAT_COV_TRIU6 ? 6 : 9;
   a.sh_floats = p.sh_coeffs > 0 ? 3 * p.sh_coeffs : 3;
   auto al16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15u) == 0; };
@@ -278,7 +282,7 @@ cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& 
   cudaError_t e = cudaFuncSetAttribute(preprocess_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                        (int)smem);
   if (e != cudaSuccess) return e;
-  dim3 grid((p.G + kPreBwdBlock - 1) / kPreBwdBlock, p.B);
+  dim3 grid((g_count + kPreBwdBlock - 1) / kPreBwdBlock, p.B);
   preprocess_backward_kernel<<<grid, kPreBwdBlock, smem, st>>>(a, ws);
   return cudaGetLastError();
 }

@@ -62,7 +62,7 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
                  image_shape: tuple, background_color: Tensor, depth_mode: Optional[str] = None,
                  scale_invariant: bool = True, want_radii: bool = False, check: Optional[str] = None,
                  use_sh: bool = True, cams: Optional[Tensor] = None, mse_target: Optional[Tensor] = None,
-                 mse_weight: float = 1.0, with_psnr: bool = False):
+                 mse_weight: float = 1.0, with_psnr: bool = False, grad_reduce=None):
     """The batched entry point.  With ``mse_target`` [b,v,3,h,w] a fourth value is returned: the reference's MSE colour
     loss ``mse_weight * ((color - target) ** 2).mean()`` (loss_mse.py:23-31), computed inside the render kernels.
   extrinsics [b,v,4,4], intrinsics [b,v,3,3], near/far [b,v],
@@ -79,7 +79,7 @@ def render_views(gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, n
                                    near.reshape(b * v), far.reshape(b * v), background_color,
                                    scale_invariant=scale_invariant)
     cfg = RenderConfig(H=h, W=w, V=v, sh_degree=degree, sh_layout=SH_G3M, cov_layout=COV_FULL9,
-                       depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check)
+                       depth_mode=DEPTH_MODES[depth_mode], want_radii=want_radii, check=check, grad_reduce=grad_reduce)
     # use_sh=False: the single coefficient is the colour itself (colors_precomp = shs[:, 0, :], cuda_splatting.py:130)
     feat = gaussians.harmonics if use_sh else gaussians.harmonics[..., 0]
     loss = psnr = None
@@ -205,9 +205,11 @@ class DecoderSplattingCUDA(nn.Module):
                              persistent=False)
 
     def forward(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,
-                image_shape: tuple, depth_mode: Optional[DepthRenderingMode] = None) -> DecoderOutput:
+                image_shape: tuple, depth_mode: Optional[DepthRenderingMode] = None, grad_reduce=None) -> DecoderOutput:
+        """decoder_splatting_cuda.py:41-73.  ``grad_reduce`` = (process group, chunks) is this library's addition for
+        view sharding (parallel.forward_view_sharded): the backward sums the gradients over the group itself."""
         color, depth, _ = render_views(gaussians, extrinsics, intrinsics, near, far, image_shape,
-                                       self.background_color, depth_mode)
+                                       self.background_color, depth_mode, grad_reduce=grad_reduce)
         return DecoderOutput(color, depth)
 
     def forward_mse(self, gaussians: Gaussians, extrinsics: Tensor, intrinsics: Tensor, near: Tensor, far: Tensor,

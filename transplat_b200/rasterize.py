@@ -109,6 +109,9 @@ class RenderConfig:
     d_cap: int | None = None
     debug: bool = False        # reference debug=True: synchronise and check after every stage
     sort: str | None = None    # None -> TSPLAT_SORT env ("bucket" default) | "bucket" | "onesweep"
+    # view sharding (parallel.py): (process group, chunks).  The backward then sums the per-Gaussian gradients over
+    # the group itself, one Gaussian range at a time, each all-reduce overlapping the next range's kernels
+    grad_reduce: tuple | None = None
 
 
 def _ptr(t):
@@ -308,20 +311,56 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
         if state.bwd_calls:
             state.problem.flags |= _lib.FLAG_REZERO_GRAD_ACC
         state.bwd_calls += 1
+        m = None
         if fused:
             target, color, scale = state.mse[:3]
             grad_loss = grad_loss.reshape(1).to(torch.float32).contiguous()
             m = TsplatMse(target=target.data_ptr(), loss_sum=0, color=color.data_ptr(), dL_dloss=grad_loss.data_ptr(),
                           scale=scale, loss_scale=0.0, psnr=0)
-            _lib.check(L.tsplat_backward_mse(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
-                                             state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means),
-                                             _ptr(g_cov), _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.byref(m),
-                                             C.c_void_p(stream.cuda_stream)), "tsplat_backward_mse")
+
+        def launch():
+            if fused:
+                _lib.check(L.tsplat_backward_mse(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
+                                                 state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means),
+                                                 _ptr(g_cov), _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.byref(m),
+                                                 C.c_void_p(stream.cuda_stream)), "tsplat_backward_mse")
+            else:
+                _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
+                                             state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
+                                             _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
+                           "tsplat_backward")
+
+        reduce = cfg.grad_reduce
+        if reduce is None or means.shape[0] != 1:
+            launch()
+            if reduce is not None:  # several scenes per call: their Gaussian ranges are not contiguous in the slab
+                import torch.distributed as dist
+                dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=reduce[0])
         else:
-            _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
-                                         state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
-                                         _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
-                       "tsplat_backward")
+            # Staged backward: the render stage fills the screen-space accumulators of all Gaussians, then
+            # the per-Gaussian stage runs range by range; the four gradient pieces of a finished range are summed over
+            # the ranks (NCCL runs on its own stream, ordered after what is enqueued here so far) while the kernels
+            # of the next range run.
+            import torch.distributed as dist
+            group, chunks = reduce
+            G = means.shape[1]
+            per = -(-G // max(int(chunks), 1))
+            step = -(-per // 64) * 64  # ranges start at multiples of 64 (the per-Gaussian kernel's CTA)
+            base_flags = state.problem.flags
+            state.problem.flags = base_flags | _lib.FLAG_BWD_RENDER_ONLY
+            launch()
+            works = []
+            for g0 in range(0, G, step):
+                g1 = min(G, g0 + step)
+                state.problem.flags = (base_flags | _lib.FLAG_BWD_GAUSSIANS_ONLY) & ~_lib.FLAG_REZERO_GRAD_ACC
+                state.problem.g_begin, state.problem.g_count = g0, g1 - g0
+                launch()
+                for t in (g_means, g_cov, g_sh, g_op):
+                    works.append(dist.all_reduce(t[0, g0:g1], op=dist.ReduceOp.SUM, group=group, async_op=True))
+            state.problem.flags = base_flags
+            state.problem.g_begin = state.problem.g_count = 0
+            for w in works:
+                w.wait()
     return g_means, g_cov, g_sh, g_op, g_m2d
 
 
