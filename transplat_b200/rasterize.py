@@ -347,20 +347,22 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
             per = -(-G // max(int(chunks), 1))
             step = -(-per // 64) * 64  # ranges start at multiples of 64 (the per-Gaussian kernel's CTA)
             base_flags = state.problem.flags
-            state.problem.flags = base_flags | _lib.FLAG_BWD_RENDER_ONLY
-            launch()
             works = []
-            for g0 in range(0, G, step):
-                g1 = min(G, g0 + step)
-                state.problem.flags = (base_flags | _lib.FLAG_BWD_GAUSSIANS_ONLY) & ~_lib.FLAG_REZERO_GRAD_ACC
-                state.problem.g_begin, state.problem.g_count = g0, g1 - g0
+            try:
+                state.problem.flags = base_flags | _lib.FLAG_BWD_RENDER_ONLY
                 launch()
-                for t in (g_means, g_cov, g_sh, g_op):
-                    works.append(dist.all_reduce(t[0, g0:g1], op=dist.ReduceOp.SUM, group=group, async_op=True))
-            state.problem.flags = base_flags
-            state.problem.g_begin = state.problem.g_count = 0
-            for w in works:
-                w.wait()
+                for g0 in range(0, G, step):
+                    g1 = min(G, g0 + step)
+                    state.problem.flags = (base_flags | _lib.FLAG_BWD_GAUSSIANS_ONLY) & ~_lib.FLAG_REZERO_GRAD_ACC
+                    state.problem.g_begin, state.problem.g_count = g0, g1 - g0
+                    launch()
+                    for t in (g_means, g_cov, g_sh, g_op):
+                        works.append(dist.all_reduce(t[0, g0:g1], op=dist.ReduceOp.SUM, group=group, async_op=True))
+            finally:  # the problem record is reused by a repeated backward over the same forward state
+                state.problem.flags = base_flags
+                state.problem.g_begin = state.problem.g_count = 0
+                for w in works:
+                    w.wait()
     return g_means, g_cov, g_sh, g_op, g_m2d
 
 
