@@ -3,8 +3,11 @@
 Independent check of the C oracle's hand-written backward: the forward math of
 SURVEY A.3/A.5/A.7 is written with differentiable torch ops in binary64 over a dense
 [pixels, Gaussians] matrix, and torch.autograd supplies the gradients.  The discrete decisions
-(visibility, tile rectangle, depth order) are taken from the C oracle's integer outputs, which is
-legitimate because they carry no gradient.  Two reference quirks are reproduced on purpose:
+(visibility, radius, tile rectangle, depth order) are computed HERE, in binary64, from the same
+definitions (``geometry`` below); tests/test_oracle_grad.py compares them with the C oracle's
+integer outputs instead of consuming those (they may legitimately differ only where a binary32
+quantity sits within rounding distance of a decision boundary, which the test bounds).
+Two reference quirks are reproduced on purpose:
   * the alpha cap min(0.99, .) is NOT masked in the reference's gradient -> straight-through;
   * colour clamp max(.,0) masks the gradient (``clamped`` flags) -> plain autograd of clamp.
 Small scenes only (memory is pixels x Gaussians).
@@ -51,10 +54,13 @@ def sh_basis(deg: int, d: torch.Tensor, sh_l4: bool = True) -> torch.Tensor:
 
 
 def render_dense(means, cov6, sh, opacity, cam: np.ndarray, H: int, W: int, sh_degree: int,
-                 radii: np.ndarray, depths: np.ndarray, depth_mode: int = 0, sh_l4: bool = True):
+                 radii: np.ndarray | None = None, depths: np.ndarray | None = None, depth_mode: int = 0,
+                 sh_l4: bool = True, geometry_out: dict | None = None):
     """means [G,3], cov6 [G,6], sh [G,M,3], opacity [G] (float64 tensors, may require grad).
-    radii/depths come from the C oracle (ordering + visibility).  Returns colour [3,H,W] and the
-    un-averaged depth channel [H,W] (or None)."""
+    With ``radii``/``depths`` None (the default) visibility, radius, tile rectangle and depth order are this
+    function's own binary64 evaluation of SURVEY A.2/A.3; ``geometry_out`` receives them (radii, radius_real,
+    visible, depths, order, rect) for comparison with the oracle.  Returns colour [3,H,W] and the un-averaged
+    depth channel [H,W] (or None)."""
     f64 = torch.float64
     c = torch.from_numpy(np.asarray(cam, np.float64))
     vm, pj = c[O_VIEW:O_VIEW + 16], c[O_PROJ:O_PROJ + 16]
@@ -65,7 +71,6 @@ def render_dense(means, cov6, sh, opacity, cam: np.ndarray, H: int, W: int, sh_d
     Pm = pj.reshape(4, 4).T                  # conventional full projection
     fx, fy = W / (2 * tanx), H / (2 * tany)
 
-    vis = torch.from_numpy(radii > 0)
     m = means * s
     S6 = cov6 * s2
     t = m @ R.T + tvec
@@ -116,12 +121,34 @@ def render_dense(means, cov6, sh, opacity, cam: np.ndarray, H: int, W: int, sh_d
         feats.append(torch.clamp(SH_C0 * f + 0.5, min=0.0)[:, None])
     feat = torch.cat(feats, -1)  # [G,CH]
 
-    # depth order (stable: ties by index) over visible Gaussians, from the oracle's float32 depths
+    gx, gy = (W + 15) // 16, (H + 15) // 16
+    if radii is None:
+        # own discrete decisions, binary64: near cull, det == 0, radius = ceil(3 sqrt(lambda_max)) with
+        # the eigenvalue floor, getRect with C truncation, zero-area rectangles culled
+        a_n, b_n, c_n, det_n = (v.detach().numpy() for v in (a, b, cc, det))
+        tz_n, px_n, py_n = tz.detach().numpy(), px.detach().numpy(), py.detach().numpy()
+        mid = 0.5 * (a_n + c_n)
+        lam = mid + np.sqrt(np.maximum(0.1, mid * mid - det_n))
+        radius_real = 3.0 * np.sqrt(np.maximum(lam, 0.0))
+        own_r = np.ceil(radius_real)
+        front = (tz_n > 0.2) & (det_n != 0.0)
+        r0 = np.where(front, own_r, 0.0)
+        tr = lambda v, hi: np.clip(np.trunc(v), 0, hi)
+        x0, y0 = tr((px_n - r0) / 16.0, gx), tr((py_n - r0) / 16.0, gy)
+        x1, y1 = tr((px_n + r0 + 15.0) / 16.0, gx), tr((py_n + r0 + 15.0) / 16.0, gy)
+        visible = front & ((x1 - x0) * (y1 - y0) > 0)
+        radii = np.where(visible, own_r, 0).astype(np.int32)
+        depths = np.where(visible, tz_n, 0.0).astype(np.float32)  # the sort key is the binary32 bit pattern
+        if geometry_out is not None:
+            geometry_out.update(radii=radii, radius_real=radius_real, visible=visible, depths=depths,
+                                rect=np.stack((x0, y0, x1, y1), -1).astype(np.int64), px=px_n, py=py_n, tz=tz_n)
+    # depth order (stable: ties by index) over visible Gaussians
     idx = np.nonzero(radii > 0)[0]
     order = idx[np.argsort(depths[idx].view(np.uint32), kind="stable")]
+    if geometry_out is not None:
+        geometry_out["order"] = order
     order_t = torch.from_numpy(order)
-    # tile-rectangle mask from the oracle's integer radii (getRect), float32 like it
-    gx, gy = (W + 15) // 16, (H + 15) // 16
+    # tile-rectangle mask (getRect)
     pxf = px.detach().numpy().astype(np.float32)[order]
     pyf = py.detach().numpy().astype(np.float32)[order]
     r = radii[order].astype(np.float32)

@@ -68,9 +68,11 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   out->zero_begin = off;
   L.status = take(sizeof(Control));
   L.ranges = take(8ull * N * T);
-  out->tile_count = take(4ull * N * T);
   out->tile_cursor = take(4ull * N * T);
   out->tile_last = take(4ull * N * T);
+  // tile_count is accumulated by the preprocess kernel itself (bucket path), so that kernel cannot also be the one
+  // that clears it: it sits last in the region and is cleared by a memset node ahead of the launch
+  out->tile_count = take(4ull * N * T);
   out->zero_mid = off;
   out->scan_state = take(8ull * out->num_scan_tiles);
   out->sort_state = take(4ull * kRadix * out->num_sort_tiles * L.sort_passes);
@@ -239,13 +241,20 @@ static int forward_impl(const TsplatProblem* p, void* workspace, uint64_t worksp
     if (e != cudaSuccess) return cuda_fail("memset(control)", e);
     ws.use_order = 0;
   } else {
-    // the preprocess kernel also zeroes the control / counters / ranges region (nothing in it is
-    // touched before the binning kernels) and the screen-space gradient accumulators of the Gaussians it keeps
+    // the preprocess kernel also zeroes the control / cursors / ranges region (nothing in it is touched before the
+    // binning kernels) and the screen-space gradient accumulators of the Gaussians it keeps.  The per-tile pair
+    // counters of the bucket path are the exception: the same launch accumulates them, and nothing orders one CTA's
+    // clear against another CTA's reduction, so they are cleared by a memset node ahead of the launch.
     ws.bucket = (p->flags & TSPLAT_FLAG_SORT_ONESWEEP) ? 0 : 1;
+    if (ws.bucket) {
+      StageTimer t(kStZero, st);
+      e = cudaMemsetAsync(static_cast<char*>(workspace) + F.tile_count, 0, F.zero_mid - F.tile_count, st);
+      if (e != cudaSuccess) return cuda_fail("memset(tile_count)", e);
+    }
     {
       StageTimer t(kStPre, st);
       e = debug_sync(p, st, launch_preprocess(*p, ws, out_radii, static_cast<char*>(workspace) + F.zero_begin,
-                                              (ws.bucket ? F.zero_mid : F.zero_end) - F.zero_begin, st));
+                                              (ws.bucket ? F.tile_count : F.zero_end) - F.zero_begin, st));
     }
     if (e != cudaSuccess) return cuda_fail("preprocess", e);
     if (ws.bucket) {
