@@ -6,7 +6,9 @@
 
 A "step" = one pass of the hot path over one batch: DecoderSplattingCUDA.forward(depth_mode="depth")
 + backward for 1 scene x 4 views per rank.  Ranks render independent scenes (scene sharding, no
-collective) => weak scaling.  One JSON line is printed by rank 0.
+collective) => weak scaling.  At N > 1 the line also carries a `view_sharded` block: ONE scene,
+4 N target views split over the ranks, per-Gaussian gradients summed with the path's only collective.
+One JSON line is printed by rank 0.
 """
 from __future__ import annotations
 
@@ -24,6 +26,8 @@ G_CTX, HW, VIEWS = 2, 256, 4          # C2: 2 context views of 256x256 -> 131072
 N_SCENES = 4                           # distinct resident scenes cycled through (4 x 46 MB of inputs)
 METRIC = "fwd+bwd views/sec (256x256, 131072 Gaussians/scene)"
 UNIT = "views/s"
+WORKLOAD = ("C2: RE10K training render step, 1 scene x 4 target views per GPU, 256x256, 131072 Gaussians (SH degree 4), "
+            "colour+depth fwd+bwd")
 
 
 def parse():
@@ -34,12 +38,29 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-view-sharded", action="store_true", help="skip the view-sharded block at N > 1")
+    ap.add_argument("--c5", action="store_true", help="at N > 1 also time the C5 stress shape view-sharded (8 views per rank)")
     ap.add_argument("--eager", action="store_true", help="launch every step from Python instead of replaying CUDA graphs")
     return ap.parse_args()
 
 
 def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+def shared_config(G: int, pairs_per_view) -> dict:
+    """The `config` object, IDENTICAL in both arms (same workload, same keys, same strings)."""
+    return {"workload": WORKLOAD, "gaussians": int(G), "views_per_step_per_gpu": VIEWS, "image": [HW, HW],
+            "sh_degree": 4, "depth_mode": "depth", "pairs_per_view": pairs_per_view,
+            "l2": "GPU arm: 256 MiB buffer zeroed between timed steps (outside the event pairs), "
+                  f"{N_SCENES} scenes cycled; CPU arm: one scene, host caches as they fall"}
+
+
+def percentiles(ms: list) -> dict:
+    s = sorted(ms)
+    pick = lambda q: s[min(len(s) - 1, max(0, int(round(q * (len(s) - 1)))))]
+    return {"median": round(pick(0.5), 4), "p10": round(pick(0.1), 4), "p90": round(pick(0.9), 4),
+            "min": round(s[0], 4), "max": round(s[-1], 4)}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -95,7 +116,6 @@ class ClockSampler:
 # workload
 # ------------------------------------------------------------------------------------------------
 def make_inputs(rank: int, n_scenes: int):
-    import torch
     from transplat_b200.synthetic import make_scene, upstream_grads
     scenes = [make_scene(n_ctx=G_CTX, h=HW, w=HW, n_views=VIEWS, seed=1236 + 100 * rank + i) for i in range(n_scenes)]
     target, dLd = upstream_grads(VIEWS, HW, HW, seed=99 + rank)
@@ -105,6 +125,49 @@ def make_inputs(rank: int, n_scenes: int):
 def bytes_per_view(G: int, D_per_view: float, P: int, T: int) -> float:
     """B_view = 1232 G + 260 D + 48 P + 8 T (fwd+bwd, colour+depth fused, fp32)."""
     return 1232.0 * G + 260.0 * D_per_view + 48.0 * P + 8.0 * T
+
+
+def timed_pass(run, steps, flush, barrier, world, dev):
+    """K steps, one CUDA-event pair per step on the launching stream, L2 flushed between steps (outside the pairs).
+    Returns (per-step ms of this rank, ms_per_step = max over ranks of the mean, host wall ms per step)."""
+    import torch
+    import torch.distributed as dist
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+    barrier()
+    t_wall = time.perf_counter()
+    for i in range(steps):
+        flush.zero_()
+        ev[i][0].record()
+        run[i % len(run)]()
+        ev[i][1].record()
+    barrier()
+    t_wall = time.perf_counter() - t_wall
+    per = [a.elapsed_time(b) for a, b in ev]
+    ms_total = sum(per)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    return per, ms_total / steps, t_wall * 1e3 / steps
+
+
+def graph_or_eager(fns, args, dev, barrier, what):
+    """One CUDA graph per callable (transplat_b200.graphs); falls back to eager launches if capture fails."""
+    import torch
+    if args.eager:
+        return list(fns), None
+    from transplat_b200.graphs import GraphedStep
+    try:
+        graphed = [GraphedStep(f, warmup=1, device=dev) for f in fns]
+        run = [g.replay for g in graphed]
+        for i in range(max(args.warmup, 3)):
+            run[i % len(run)]()
+        barrier()
+        return run, graphed
+    except Exception as exc:  # never lose the measurement to a capture problem
+        print(f"[bench] CUDA-graph capture of {what} failed ({exc!r}); launching eagerly", file=sys.stderr, flush=True)
+        torch.cuda.synchronize()
+        return list(fns), None
 
 
 def run_ours(args):
@@ -122,11 +185,11 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()  # fail loudly if libtsplat.so is missing
 
+    W = max(args.warmup, 3)
     scenes, target_h, dLd_h = make_inputs(rank, N_SCENES)
     G = scenes[0].means.shape[0]
     P, T = HW * HW, (HW // 16) ** 2
     decoder = DecoderSplattingCUDA().to(dev)
-    numel = float(VIEWS * 3 * HW * HW)
 
     def to_dev(sc):
         leaf = lambda t: t.to(dev)
@@ -137,7 +200,6 @@ def run_ours(args):
     dev_scenes = [to_dev(s) for s in scenes]
     target = target_h[None].to(dev)
     dLd = dLd_h[None].to(dev)
-
     one = torch.ones((), device=dev)
 
     def step(s):
@@ -149,6 +211,15 @@ def run_ours(args):
         grads = torch.autograd.grad([loss, out.depth], leaves, [one, dLd])
         return out, loss, grads, loss.grad_fn.state if hasattr(loss.grad_fn, "state") else None
 
+    def step_dropin(s):
+        # the plain drop-in surface: DecoderSplattingCUDA.forward(depth_mode="depth") as the reference calls it
+        # (decoder_splatting_cuda.py:41-73) + LossMse as torch ops (loss_mse.py:23-31) + backward
+        leaves = [s[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
+        out = decoder.forward(Gaussians(*leaves), s["ext"], s["intr"], s["near"], s["far"], (HW, HW), depth_mode="depth")
+        loss = ((out.color - target) ** 2).mean()
+        grads = torch.autograd.grad([loss, out.depth], leaves, [one, dLd])
+        return out, loss, grads
+
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def barrier():
@@ -156,45 +227,34 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(max(args.warmup, 3)):
+    for i in range(W):
         step(dev_scenes[i % N_SCENES])
     barrier()
     # one CUDA graph per resident scene (transplat_b200.graphs): a step is then ONE launch.  Eagerly the host needs
     # 0.3-0.45 ms per step, which starves the GPUs once 8 ranks share the box's 16 vCPUs.
-    run = [(lambda sc=sc: step(sc)) for sc in dev_scenes]
-    if not args.eager:
-        from transplat_b200.graphs import GraphedStep
-        try:
-            graphed = [GraphedStep(f, warmup=1, device=dev) for f in run]
-            run = [g.replay for g in graphed]
-            for i in range(max(args.warmup, 3)):
-                run[i % N_SCENES]()
-        except Exception as exc:  # never lose the measurement to a capture problem: fall back to eager launches
-            print(f"[bench] CUDA-graph capture failed ({exc!r}); launching eagerly", file=sys.stderr, flush=True)
-            args.eager = True
-            torch.cuda.synchronize()
-            run = [(lambda sc=sc: step(sc)) for sc in dev_scenes]
-        barrier()
+    run, graphed = graph_or_eager([(lambda sc=sc: step(sc)) for sc in dev_scenes], args, dev, barrier, "the step")
+    if graphed is None:
+        args.eager = True
 
     # ---- timed region: device-resident inputs, one CUDA-event pair per step, L2 flushed between steps.
     # No per-stage events in here: recording an event between every two kernels of the chain costs 4 % of the step
     # (measured, profiles/r01_experiments.md); the per-kernel durations for the roofline come from a second pass.
     sampler = ClockSampler(local_rank)
     sampler.start()
-    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
-    barrier()
-    t_wall = time.perf_counter()
-    for i in range(args.steps):
-        flush.zero_()
-        ev[i][0].record()
-        run[i % N_SCENES]()
-        ev[i][1].record()
-    barrier()
-    t_wall = time.perf_counter() - t_wall
-    if not args.eager:  # the pair list of a replayed step must not have overflowed its captured capacity
+    per_step, ms_per_step, host_wall = timed_pass(run, args.steps, flush, barrier, world, dev)
+    if graphed is not None:  # the pair list of a replayed step must not have overflowed its captured capacity
         from transplat_b200.rasterize import read_status_device
         for gs in graphed:
             assert read_status_device(gs.outputs[3]).overflow == 0, "pair-list overflow inside a captured step"
+    value = world * VIEWS / (ms_per_step * 1e-3)
+
+    # ---- the same K steps through the plain drop-in call surface (no fused loss)
+    for i in range(W):
+        step_dropin(dev_scenes[i % N_SCENES])
+    barrier()
+    run_d, _ = graph_or_eager([(lambda sc=sc: step_dropin(sc)) for sc in dev_scenes], args, dev, barrier, "the drop-in step")
+    per_step_d, ms_dropin, _ = timed_pass(run_d, args.steps, flush, barrier, world, dev)
+
     # ---- same K steps again with the library's per-stage events on the launching stream (roofline.stage_ms)
     _lib.profile_enable(True)
     for i in range(args.steps):
@@ -203,27 +263,23 @@ def run_ours(args):
     barrier()
     stages = _lib.profile_read()
     _lib.profile_enable(False)
-    ms_total = sum(a.elapsed_time(b) for a, b in ev)
-    if world > 1:
-        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total = float(t.item())
-    ms_per_step = ms_total / args.steps
-    value = world * VIEWS / (ms_per_step * 1e-3)
 
-    # measured pair count D (per call = all 4 views) of the last step
+    # measured pair count D (per call = all 4 views) of scene 0 (the scene the CPU arm renders)
     from transplat_b200.rasterize import _capacity
-    D_call = None
-    for key in list(_capacity.pending):
-        st = _capacity.poll(key, wait=True)
-        if st is not None:
-            D_call = int(st.num_rendered)
+    _capacity.sweep(wait=True)
+    step(dev_scenes[0])
+    _capacity.sweep(wait=True)
+    D_call = _capacity.last_num_rendered
 
     # ---- end to end through the public API with HOST buffers (H2D + D2H inside the timed region)
     e2e = None
     if not args.no_e2e:
         e2e = run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world)
-    clocks = sampler.stop()  # sampled over the timed pass, the per-stage pass and the e2e leg
+    # ---- the path's only collective: one scene, its views split over the ranks
+    view_sharded = None
+    if world > 1 and not args.no_view_sharded:
+        view_sharded = run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_per_step)
+    clocks = sampler.stop()  # sampled over the timed passes, the per-stage pass, the e2e leg and the view-sharded leg
 
     if rank != 0:
         if world > 1:
@@ -246,30 +302,41 @@ def run_ours(args):
     top_bytes = alg[top] * VIEWS
     achieved = top_bytes / (kern[top] * 1e-3) / 1e9 if kern[top] > 0 else 0.0
     step_bytes = bytes_per_view(G, Dv, P, T) * VIEWS
-    traffic = load_traffic(top)
+    traffic, traffic_src = load_traffic(top)
+
+    def stage_entry(k):
+        t, _ = load_traffic(k)
+        d = {"ms": round(kern[k], 4), "algorithmic_bytes": round(alg[k] * VIEWS),
+             "achieved": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9, 1) if kern[k] > 0 else None,
+             "frac": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9 / peak, 4) if kern[k] > 0 else None,
+             "traffic": t, **load_issue(k)}
+        # what the kernel actually moves through DRAM (ncu dram__bytes per launch) over its measured duration
+        d["achieved_dram_gbs"] = round(t / (kern[k] * 1e-3) / 1e9, 1) if (t and kern[k] > 0) else None
+        return d
+
     line = {
         "metric": METRIC, "value": round(value, 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
+        "warmup": W, "ms_per_step": round(ms_per_step, 4), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "C2: RE10K training render step, 1 scene x 4 target views per GPU, 256x256, "
-                               "131072 Gaussians (SH degree 4), colour+depth fwd+bwd",
-                   "gaussians": G, "views_per_step_per_gpu": VIEWS, "pairs_per_view": round(Dv),
-                   "parallelism": f"scene-sharded x{world} (no collective)",
-                   "l2": "256 MiB buffer zeroed between timed steps (outside the event pairs); "
-                         f"{N_SCENES} scenes cycled",
-                   "api": "DecoderSplattingCUDA.forward_mse(depth_mode='depth') [render + fused MSE colour loss] + torch.autograd.grad"
-                          + ("" if args.eager else ", captured once per resident scene in a CUDA graph (transplat_b200.graphs) and replayed")},
+        "config": shared_config(G, round(Dv)),
+        "details": {"parallelism": f"scene-sharded x{world} (no collective)",
+                    "api": "DecoderSplattingCUDA.forward_mse(depth_mode='depth') [render + fused MSE colour loss] + torch.autograd.grad"
+                           + ("" if args.eager else ", captured once per resident scene in a CUDA graph (transplat_b200.graphs) and replayed")},
+        "step_ms": percentiles(per_step),
+        "gaussians_per_s": round(world * VIEWS * G / (ms_per_step * 1e-3)),
+        "dropin": {"value": round(world * VIEWS / (ms_dropin * 1e-3), 2), "unit": UNIT, "ms_per_step": round(ms_dropin, 4),
+                   "step_ms": percentiles(per_step_d),
+                   "api": "DecoderSplattingCUDA.forward(depth_mode='depth') + ((color - target) ** 2).mean() as torch ops + "
+                          "torch.autograd.grad: the reference's call surface with nothing fused after it"},
         "clocks": clocks,
         "e2e": e2e,
         "gpu_launches": args.steps * launches_per_step(VIEWS, T),
         "roofline": {"bound": "hbm", "kernel": top, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-                     "frac": round(achieved / peak, 4), "traffic": traffic, "peak_source": peak_src,
+                     "frac": round(achieved / peak, 4), "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_launch": round(top_bytes), "kernel_ms": round(kern[top], 4),
                      "stage_ms": {k: round(v, 4) for k, v in stages.items()},
-                     "per_stage": {k: {"ms": round(kern[k], 4), "algorithmic_bytes": round(alg[k] * VIEWS),
-                                       "achieved": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9, 1) if kern[k] > 0 else None,
-                                       "frac": round(alg[k] * VIEWS / (kern[k] * 1e-3) / 1e9 / peak, 4) if kern[k] > 0 else None,
-                                       "traffic": load_traffic(k), **load_issue(k)} for k in alg},
+                     "per_stage": {k: stage_entry(k) for k in alg},
                      "issue": {"what": "the two render kernels have no dense contraction and move little memory: "
                                        "they are bound by instruction issue (ncu --set full capture of this command, "
                                        "profiles/traffic.json: smsp__issue_active, smsp__inst_executed per launch)",
@@ -279,8 +346,10 @@ def run_ours(args):
                      "step": {"algorithmic_bytes": round(step_bytes),
                               "achieved": round(step_bytes / (ms_per_step * 1e-3) / 1e9, 1),
                               "frac": round(step_bytes / (ms_per_step * 1e-3) / 1e9 / peak, 4)}},
-        "host_wall_ms_per_step": round(t_wall * 1e3 / args.steps, 4),
+        "host_wall_ms_per_step": round(host_wall, 4),
     }
+    if view_sharded is not None:
+        line["view_sharded"] = view_sharded
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(scenes[0], target_h, dLd_h, budget_s=12.0)
     print(json.dumps(line), flush=True)
@@ -291,7 +360,8 @@ def run_ours(args):
 def launches_per_step(n_views: int, T: int) -> int:
     """Kernels of libtsplat.so launched per step (the MSE colour loss runs inside the render kernels).
     bucket path (default): pack_cameras, preprocess_forward, bucket_scan, bucket_emit, tile_sort_gather,
-    big_tile_sort_gather, gather_records, render_forward, status_store, render_backward, preprocess_backward = 11;
+    big_tile_sort_gather, gather_records, render_forward, status_store, render_backward, preprocess_backward = 11
+    (the memset node that clears the per-tile pair counters is not a kernel of the library and is not counted);
     onesweep path: pack_cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd/bwd, preprocess bwd."""
     if os.environ.get("TSPLAT_SORT", "bucket") == "onesweep":
         return 8 + sort_passes(n_views, T)
@@ -304,12 +374,13 @@ def sort_passes(n_views: int, T: int) -> int:
 
 
 def load_traffic(kernel: str):
-    """dram bytes per launch of the dominant kernel from the committed `ncu --set full` summary."""
+    """(dram bytes per launch, where the number comes from) of a kernel.  The bytes are NOT measured in this run: they
+    are read from the committed summary of an `ncu --set full` capture of this same command (profiles/traffic.json)."""
     try:
         d = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        return d.get(kernel)
+        return d.get(kernel), "profiles/traffic.json (" + d.get("_source", "ncu --set full capture of this command") + ")"
     except Exception:
-        return None
+        return None, None
 
 
 def load_issue(kernel: str) -> dict:
@@ -405,40 +476,130 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
 
 
 # ------------------------------------------------------------------------------------------------
+# view sharding (BASELINE configs 4b and 5): ONE scene replicated on every rank, its target views split
+# over the ranks, per-Gaussian gradients (85 floats per Gaussian) summed with the path's only collective.
+# ------------------------------------------------------------------------------------------------
+def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_sharded):
+    import torch
+    import torch.distributed as dist
+    from transplat_b200.decoder import Gaussians
+    from transplat_b200.parallel import forward_view_sharded
+    from transplat_b200.synthetic import make_scene, upstream_grads
+
+    def one_shape(name, hw, per_rank, steps, chunks):
+        V = per_rank * world
+        sc = make_scene(n_ctx=G_CTX, h=hw, w=hw, n_views=V, seed=4242)   # the same scene on every rank
+        tgt, dd = upstream_grads(V, hw, hw, seed=7)
+        mine = list(range(rank, V, world))
+        tgt, dd = tgt[mine][None].to(dev), dd[mine][None].to(dev)
+        G = sc.means.shape[0]
+        stat = dict(means=sc.means[None].to(dev), cov=sc.covariances[None].to(dev), sh=sc.harmonics[None].to(dev),
+                    op=sc.opacities[None].to(dev))
+        cam = [t[None].to(dev) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
+        one = torch.ones((), device=dev)
+
+        def step(reduce=True, overlap=0):
+            leaves = [stat[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
+            g = Gaussians(*leaves)
+            if reduce:
+                out, _ = forward_view_sharded(decoder, g, *cam, (hw, hw), depth_mode="depth", overlap_chunks=overlap)
+            else:  # the same local views, no collective: what the step costs without the exchange
+                idx = torch.tensor(mine, device=dev)
+                out = decoder.forward(g, *(c[:, idx] for c in cam), (hw, hw), depth_mode="depth")
+            loss = ((out.color - tgt) ** 2).mean()
+            return torch.autograd.grad([loss, out.depth], leaves, [one, dd])
+
+        def time_it(fn, k):
+            for _ in range(3):
+                fn()
+            ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(k)]
+            barrier()
+            for i in range(k):
+                flush.zero_()
+                ev[i][0].record()
+                fn()
+                ev[i][1].record()
+            barrier()
+            t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev) / k], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        t_plain = time_it(lambda: step(True, 0), steps)
+        t_overlap = time_it(lambda: step(True, chunks), steps) if chunks > 1 else None
+        t_local = time_it(lambda: step(False), steps)
+        # the collective alone, on a slab of the same size
+        from transplat_b200.rasterize import _pad64
+        n_slab = _pad64(G * 3) + _pad64(G * 9) + _pad64(G * 75) + G
+        slab = torch.zeros(n_slab, dtype=torch.float32, device=dev)
+        t_ar = time_it(lambda: dist.all_reduce(slab), max(steps, 10))
+        best = min(t for t in (t_plain, t_overlap) if t is not None)
+        nbytes = n_slab * 4
+        return {"shape": name, "views": V, "views_per_rank": per_rank, "gaussians": G, "image": [hw, hw], "steps": steps,
+                "ms_per_step": round(best, 4), "views_per_s": round(V / (best * 1e-3), 1),
+                "ms_per_step_one_all_reduce": round(t_plain, 4),
+                "ms_per_step_chunked_overlap": round(t_overlap, 4) if t_overlap is not None else None, "chunks": chunks,
+                "ms_per_step_without_collective": round(t_local, 4),
+                "all_reduce_exposed_ms": round(best - t_local, 4),
+                "all_reduce_alone_ms": round(t_ar, 4), "all_reduce_bytes": int(nbytes),
+                "all_reduce_bus_gbs": round(2.0 * (world - 1) / world * nbytes / (t_ar * 1e-3) / 1e9, 1),
+                "launch": "eager (one process per GPU, NCCL on its own stream)"}
+
+    out = {"what": "one scene, target views split round-robin over the ranks, Gaussians replicated, per-Gaussian gradients "
+                   "summed over the ranks (ncclAllReduce, float32 sum): the only collective on the path (SURVEY 8e); "
+                   "fwd+bwd through transplat_b200.parallel.forward_view_sharded, device time, max over ranks",
+           "c2_shape": one_shape("C2 shape: 131072 Gaussians, 256x256, 4 views per rank", HW, VIEWS, min(args.steps, 30), 2)}
+    if args.c5:
+        out["c5_shape"] = one_shape("C5 stress: 2097152 Gaussians, 1024x1024, 8 views per rank", 1024, 8, 5, 3)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # CPU arm: the oracle port (oracle/tsplat_oracle.c, OpenMP) on the host cores.  The reference's own
 # arithmetic lives in an external extension whose source is absent, so "reference" here
 # is the port, kind "port".
 # ------------------------------------------------------------------------------------------------
+def oracle_threads() -> int:
+    """All the host cores this process may use, set explicitly: torch.distributed.run exports OMP_NUM_THREADS=1."""
+    import oracle
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        n = os.cpu_count() or 1
+    return oracle.set_num_threads(n)
+
+
 def oracle_step(scene, target, dLd):
-    """One C2 step on the CPU: 4 views colour+depth forward, MSE gradient, backward summed over views."""
+    """One C2 step on the CPU: 4 views colour+depth forward, MSE gradient, backward summed over views.
+    Returns (gradient accumulators, pairs per view)."""
     import numpy as np
     import torch
     import oracle
     from transplat_b200.cameras import pack_cameras
 
-    G = scene.means.shape[0]
     cams = pack_cameras(scene.extrinsics, scene.intrinsics, scene.near, scene.far, torch.zeros(VIEWS, 3)).numpy()
     sc = oracle.Scene(scene.means.numpy(), scene.covariances.numpy(), scene.harmonics.numpy(), scene.opacities.numpy(),
                       4, oracle.SH_G3M, oracle.COV_FULL9)
     acc = oracle.GradAccum(sc)
     numel = float(VIEWS * 3 * HW * HW)
     tgt, dd = target.numpy(), dLd.numpy()
+    pairs = 0
     for v in range(VIEWS):
         st = oracle.forward(sc, cams[v], HW, HW, depth_mode="depth")
+        pairs += st.num_rendered
         dLc = (st.color - tgt[v]) * np.float32(2.0 / numel)
         oracle.backward(sc, cams[v], st, dLc, dd[v], acc=acc, depth_mode="depth")
-    return acc
+    return acc, pairs / VIEWS
 
 
 def cpu_baseline(scene, target, dLd, budget_s: float):
-    import oracle
+    cores = oracle_threads()
     oracle_step(scene, target, dLd)  # warm-up (builds the library, pages it in)
     t0, n = time.perf_counter(), 0
     while n < 1 or (time.perf_counter() - t0 < budget_s and n < 16):
         oracle_step(scene, target, dLd)
         n += 1
     dt = time.perf_counter() - t0
-    return {"value": round(n * VIEWS / dt, 3), "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+    return {"value": round(n * VIEWS / dt, 3), "unit": UNIT, "cores": cores, "kind": "port",
             "sample": f"{n} full C2 steps (1 scene x {VIEWS} views fwd+bwd, colour+depth) of the same workload, "
                       f"oracle/tsplat_oracle.c with OpenMP, {dt:.1f} s"}
 
@@ -447,23 +608,30 @@ def run_reference(args):
     rank, _, world = dist_env()
     if rank != 0:
         return
-    import oracle
+    cores = oracle_threads()
+    W = max(args.warmup, 3)
     scenes, target, dLd = make_inputs(0, 1)
-    for _ in range(max(1, min(args.warmup, 3))):
-        oracle_step(scenes[0], target, dLd)
-    t0 = time.perf_counter()
+    pairs = 0
+    for _ in range(W):
+        _, pairs = oracle_step(scenes[0], target, dLd)
+    per = []
     for _ in range(args.steps):
+        t0 = time.perf_counter()
         oracle_step(scenes[0], target, dLd)
-    dt = time.perf_counter() - t0
+        per.append((time.perf_counter() - t0) * 1e3)
+    dt = sum(per) * 1e-3
     value = args.steps * VIEWS / dt
+    G = int(scenes[0].means.shape[0])
     line = {"impl": "reference", "metric": METRIC, "value": round(value, 3), "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": max(1, min(args.warmup, 3)), "ms_per_step": round(dt * 1e3 / args.steps, 3),
+            "steps": args.steps, "warmup": W, "ms_per_step": round(dt * 1e3 / args.steps, 3),
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "C2: RE10K training render step, 1 scene x 4 target views, 256x256, 131072 Gaussians "
-                                   "(SH degree 4), colour+depth fwd+bwd", "gaussians": int(scenes[0].means.shape[0]),
-                       "note": "CPU port of the rasterizer (the reference's own CUDA extension is an unpinned external "
-                               "dependency whose source is absent); rank 0 only, host cores"},
-            "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
+            "config": shared_config(G, round(pairs)),
+            "details": {"note": "CPU port of the rasterizer (the reference's own CUDA extension is an unpinned external "
+                                "dependency whose source is absent: the ref-CUDA arm is not available on this box); rank 0 "
+                                "only, all host cores (OpenMP team set explicitly)"},
+            "step_ms": percentiles(per),
+            "gaussians_per_s": round(VIEWS * G / (dt / args.steps)),
+            "cpu_baseline": {"value": round(value, 3), "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": f"{args.steps} full C2 steps, {dt:.1f} s"},
             "e2e": {"value": round(value, 3), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)

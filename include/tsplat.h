@@ -217,6 +217,16 @@ int tsplat_backward_mse(const TsplatProblem* p, void* workspace, uint64_t worksp
 int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix,
                         const float* projmatrix, uint8_t* present, void* cuda_stream);
 
+/* The scales / rotations input mode of GaussianRasterizer.forward ("exactly one of (scales, rotations) /
+ * cov3D_precomp"): computeCov3D of the extension and its backward.  scales [G,3], rotations [G,4] as (r, x, y, z), used
+ * as given (the extension does not normalise the quaternion); cov6 [G,6] = upper triangle of R diag(s^2) R^T with
+ * s = scale_modifier * scale.  TranSplat always passes cov3D_precomp (cuda_splatting.py:124,132); at the reference's
+ * call sites scale_modifier is 1.0 (cuda_splatting.py:114). */
+int tsplat_cov3d_forward(int32_t G, const float* scales, const float* rotations, float scale_modifier, float* cov6,
+                         void* cuda_stream);
+int tsplat_cov3d_backward(int32_t G, const float* scales, const float* rotations, float scale_modifier,
+                          const float* dL_dcov6, float* dL_dscales, float* dL_drotations, void* cuda_stream);
+
 /* Device-side camera preparation for the batched decoder path: fills cams[N]
  * from what DecoderSplattingCUDA.forward receives, in one launch and with no host synchronisation.
  * Replaces the host arithmetic of render_cuda / render_depth_cuda:

@@ -65,6 +65,12 @@ def num_threads() -> int:
     return int(lib().oracle_num_threads())
 
 
+def set_num_threads(n: int) -> int:
+    """OpenMP team size of the oracle (torch.distributed.run exports OMP_NUM_THREADS=1 to its ranks)."""
+    lib().oracle_set_num_threads(C.c_int(int(n)))
+    return num_threads()
+
+
 def higher_msb(n: int) -> int:
     return int(lib().oracle_higher_msb(C.c_uint32(n)))
 

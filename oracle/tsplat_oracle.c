@@ -16,8 +16,10 @@
  *   /root/reference/src/model/decoder/cuda_splatting.py:73-96    (scale invariance, matrices)
  *   /root/reference/src/model/decoder/cuda_splatting.py:375-417  (depth = a degree-0 colour pass)
  *   /root/reference/src/model/encoder/matching/conversions.py:17-27 (relative disparity)
- * The oracle is pinned only by closed-form known-answer tests (tests/test_oracle_kat.py) and by a
- * float64 dense autograd formulation of the same math (oracle/torch_dense.py).
+ * The oracle is pinned only by the closed-form known-answer tests of tests/kat.py (run through this file by
+ * tests/test_oracle_kat.py and through the CUDA library by tests/test_gpu_kat.py) and by a float64 dense autograd
+ * formulation of the same math that takes its own discrete decisions (oracle/torch_dense.py,
+ * tests/test_oracle_grad.py).
  *
  * Floating-point contract: every quantity that feeds an integer decision (depth bits, radius,
  * tile rectangle, tiles_touched) is computed in IEEE binary32, one rounding per operation,
@@ -689,6 +691,17 @@ void oracle_mark_visible(int G, const float* means, const float* view, uint8_t* 
     transform4x3(means + 3 * (size_t)i, view, pv);
     present[i] = pv[2] > 0.2f;
   }
+}
+
+/* OpenMP team size.  torch.distributed.run exports OMP_NUM_THREADS=1 to every rank; the timed CPU arm of bench.py
+ * sets the count it wants explicitly instead of inheriting that. */
+void oracle_set_num_threads(int n) {
+#ifdef _OPENMP
+  extern void omp_set_num_threads(int);
+  if (n > 0) omp_set_num_threads(n);
+#else
+  (void)n;
+#endif
 }
 
 int oracle_num_threads(void) {

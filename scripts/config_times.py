@@ -78,8 +78,7 @@ def run(name):
     _lib.profile_enable(False)
     calls = max(int(st.get("calls", 1)), 1)
     from transplat_b200 import rasterize as rz
-    for k in list(rz._capacity.pending):
-        rz._capacity.poll(k, wait=True)
+    rz._capacity.sweep(wait=True)
     D = rz._capacity.last_num_rendered
     peaks = {}
     try:

@@ -45,6 +45,15 @@ def case(name: str):
     if name == "c2":               # BASELINE config 2: 131072 Gaussians, 4 views, 256x256, colour+depth
         sc = make_scene()
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))
+    if name == "c3_two_scenes":    # BASELINE config 3 shape: a batch of scenes at full size in ONE call (2 x 131072 x 4 views)
+        sc = make_scene()
+        return _pack(sc, level=2, B=2, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))
+    if name == "c4b_video":        # BASELINE config 4b: the re10k video index, 67 target views of one scene in ONE call
+        sc = make_scene(n_views=67, seed=43)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))
+    if name == "c5_stress":        # BASELINE config 5: 2 097 152 Gaussians at 1024x1024 (2 of the 64 views)
+        sc = make_scene(n_ctx=2, h=1024, w=1024, n_views=2, seed=55)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))
     raise KeyError(name)
 
 

@@ -98,8 +98,9 @@ def compare_backward(grads, accs) -> dict:
     return rep
 
 
-def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=True, seed=7):
-    """Everything on the same seeded inputs.  Returns (forward report, backward report|None)."""
+def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=True, seed=7, oracle_cache=None):
+    """Everything on the same seeded inputs.  Returns (forward report, backward report|None).  ``oracle_cache`` (a dict)
+    keeps the oracle's result between calls that differ only in the CUDA binning path."""
     dev = torch.device("cuda:0")
     cfg.check = "sync"
     gm, gc, gs, go, gcam = (t.to(dev) for t in (means, cov, sh, opacity, cams))
@@ -109,7 +110,12 @@ def run_both(means, cov, sh, opacity, cams, cfg: RenderConfig, with_backward=Tru
     g = torch.Generator().manual_seed(seed)
     dLc = torch.randn(N, 3, cfg.H, cfg.W, generator=g)
     dLd = torch.randn(N, cfg.H, cfg.W, generator=g)
-    states, accs = oracle_batch(means, cov, sh, opacity, cams, cfg, dLc if with_backward else None, dLd)
+    if oracle_cache is not None and "states" in oracle_cache:
+        states, accs = oracle_cache["states"], oracle_cache["accs"]
+    else:
+        states, accs = oracle_batch(means, cov, sh, opacity, cams, cfg, dLc if with_backward else None, dLd)
+        if oracle_cache is not None:
+            oracle_cache.update(states=states, accs=accs)
     fwd = compare_forward(ins, color, depth, states, cfg)
     if radii is not None:
         fwd["out_radii_mismatch"] = int(sum((radii[n].cpu().numpy() != st.radii).sum() for n, st in enumerate(states)))

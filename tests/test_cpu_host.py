@@ -129,3 +129,48 @@ def test_ply_export_matches_reference_table(tmp_path):
     assert table.shape == z["table"].shape
     # quaternions are sign-ambiguous only through scipy's canonicalisation, which both sides share
     assert np.abs(table - z["table"]).max() <= 1e-5 * np.abs(z["table"]).max()
+
+
+def test_unmodified_reference_file_marshals_like_the_batched_path(monkeypatch):
+    """The UNMODIFIED reference file src/model/decoder/cuda_splatting.py, imported with this repository's
+    `diff_gaussian_rasterization` package in place of the extension, reaches the library call (here intercepted: no
+    GPU) with exactly the per-view camera record, scaled means / covariances and SH layout that the batched level-2
+    path hands to the same library call for the same inputs.  (The GPU twin,
+    tests/test_gpu_parity.py::test_unmodified_reference_file_through_the_shim, renders through it.)"""
+    ref_root = os.environ.get("TSPLAT_REFERENCE_ROOT", "/root/reference")
+    if not os.path.exists(os.path.join(ref_root, "src", "model", "decoder", "cuda_splatting.py")):
+        pytest.skip("reference tree not present on this machine")
+    import diff_gaussian_rasterization as shim
+    import transplat_b200.rasterizer as level1
+    from oracle.rasterizer_cpu import load_reference_cuda_splatting
+    calls = []
+
+    def fake_rasterize(means, cov, feat, opacity, cam, cfg, means2d=None):
+        calls.append(dict(means=means.clone(), cov=cov.clone(), feat=feat.clone(), opacity=opacity.clone(),
+                          cam=cam.clone(), cfg=cfg))
+        return (torch.zeros(1, 3, cfg.H, cfg.W), None, torch.zeros(1, means.shape[1], dtype=torch.int32))
+
+    monkeypatch.setattr(level1, "rasterize", fake_rasterize)
+    ref = load_reference_cuda_splatting(shim, ref_root)
+    z = np.load(GOLD)
+    t = lambda k: torch.from_numpy(z[k])
+    V = z["extrinsics"].shape[0]
+    H, W = z["color"].shape[-2:]
+    rep = lambda k: t(k)[None].expand(V, *z[k].shape)
+    out = ref.render_cuda(t("extrinsics"), t("intrinsics"), t("near"), t("far"), (H, W), t("bg")[None].expand(V, 3),
+                          rep("means"), rep("cov"), rep("harmonics"), rep("opacities"))
+    assert tuple(out.shape) == (V, 3, H, W) and len(calls) == V
+    cams = pack_cameras(t("extrinsics"), t("intrinsics"), t("near"), t("far"), t("bg")[None].expand(V, 3))
+    row, col = torch.triu_indices(3, 3)
+    for v, c in enumerate(calls):
+        cfg = c["cfg"]
+        assert (cfg.H, cfg.W, cfg.V, cfg.sh_degree, cfg.depth_mode, cfg.want_radii) == (H, W, 1, 4, 0, True)
+        cam = c["cam"][0]
+        # view / projection / camera position / tan(fov/2) / background: the values the batched packer produces
+        assert torch.equal(cam[:40], cams[v, :40])
+        assert float(cam[40]) == 1.0 and float(cam[41]) == 1.0  # level 1: the reference file has already scaled the scene
+        s = cams[v, 40]
+        assert torch.equal(c["means"][0], t("means") * s)
+        assert torch.equal(c["cov"][0], (t("cov") * s ** 2)[:, row, col])
+        assert torch.equal(c["feat"][0], t("harmonics").permute(0, 2, 1))   # [G, M, 3]
+        assert torch.equal(c["opacity"][0], t("opacities"))

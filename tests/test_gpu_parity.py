@@ -79,50 +79,140 @@ def test_c4_dtu_full_size_parity():
     _assert_reports(fwd, bwd)
 
 
-def test_c5_stress_both_binning_paths_agree():
-    """BASELINE config 5 shape (2 097 152 Gaussians at 1024x1024), 2 views: too large for the CPU oracle to be quick,
-    so the two independent binning paths (per-tile bucket sort; global onesweep radix sort) are held to each other
-    bit for bit (keys, values, ranges), images to 1e-6, gradients to 1e-5; oracle parity of both is shown at the
-    smaller sizes."""
-    from transplat_b200.rasterize import backward_raw, forward_raw, inspect_workspace
-    from transplat_b200.synthetic import make_scene
-    sc = make_scene(n_ctx=2, h=1024, w=1024, n_views=2, seed=55)
-    means, cov, sh, op, cams, cfg = _pack_c5(sc)
-    g = torch.Generator().manual_seed(1)
-    dLc = torch.randn(2, 3, 1024, 1024, generator=g).cuda()
-    dLd = torch.randn(2, 1024, 1024, generator=g).cuda()
-    res = {}
-    for sort in ("bucket", "onesweep"):
-        cfg.sort, cfg.check = sort, "sync"
-        color, depth, radii, state = forward_raw(cfg, means, cov, sh, op, cams)
-        ins = inspect_workspace(state)
-        assert ins["overflow"] == 0 and ins["num_rendered"] > 4_000_000
-        grads = backward_raw(cfg, state, dLc, dLd)
-        res[sort] = (ins["keys"].clone(), ins["vals"].clone(), ins["ranges"].clone(), color, depth, [x.clone() for x in grads[:4]])
-        del state
-    a, b = res["bucket"], res["onesweep"]
-    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
-    ne = (a[2][..., 1] > a[2][..., 0])
-    assert torch.equal(a[2][ne], b[2][ne]) and torch.equal(ne, b[2][..., 1] > b[2][..., 0])
-    assert float((a[3] - b[3]).abs().max()) <= 1e-6 and float((a[4] - b[4]).abs().max()) <= 1e-6
-    for x, y in zip(a[5], b[5]):
-        assert float((x - y).abs().max()) <= 1e-5 * float(y.abs().max())
-    # sortedness: keys ascending inside every tile range (size-independent property of the path)
-    k = a[0]
-    assert bool((k[1:] >= k[:-1]).all())
+@pytest.mark.parametrize("sort", ["bucket", "onesweep"])
+def test_c5_stress_full_size_oracle_parity(sort, _c5_cache={}):
+    """BASELINE config 5 at full size against the CPU oracle: 2 097 152 Gaussians at 1024x1024, 2 of the 64 target
+    views, fwd + bwd, both binning paths (45-bit keys, ~13 M pairs).  The OpenMP oracle needs a few seconds per view;
+    its result is computed once and shared by the two parametrisations."""
+    *args, cfg = case("c5_stress")
+    cfg.sort, cfg.want_radii = sort, False
+    fwd, bwd = run_both(*args, cfg, oracle_cache=_c5_cache)
+    assert fwd["num_rendered_gpu"] > 8_000_000
+    _assert_reports(fwd, bwd)
 
 
-def _pack_c5(sc):
+def test_c4b_video_67_views_in_one_call():
+    """BASELINE config 4b (re10k video index: mean 67 target views per scene) as ONE library call: 17 152 (view, tile)
+    ids, 47 key bits; forward colour + depth against the oracle (evaluation has no backward)."""
+    *args, cfg = case("c4b_video")
+    cfg.want_radii = False
+    fwd, _ = run_both(*args, cfg, with_backward=False)
+    assert fwd["views"] == 67 and fwd["num_rendered_gpu"] > 20_000_000
+    _assert_reports(fwd, None)
+
+
+def test_c3_batch_of_scenes_full_size():
+    """BASELINE config 3 shape: a batch of scenes at full size in one call (B = 2 x 131072 Gaussians x 4 views);
+    gradients stay per scene."""
+    fwd, bwd = run_both(*case("c3_two_scenes"))
+    assert fwd["views"] == 8
+    _assert_reports(fwd, bwd)
+
+
+def test_many_tiles_bucket_path_matches_onesweep():
+    """7 views of 2048x2048 = 114 688 (view, tile) ids with 131 072 Gaussians: the per-tile pair counters span far more
+    memory than the first wave of preprocess CTAs clears, so a clear that raced with the accumulation (the round-1
+    layout) would shorten ranges here.  The two independent binning paths must agree bit for bit, and the pair count
+    must equal the sum of tiles_touched."""
     from transplat_b200._lib import COV_FULL9, SH_G3M
     from transplat_b200.cameras import pack_cameras_device
-    from transplat_b200.rasterize import RenderConfig
+    from transplat_b200.rasterize import RenderConfig, forward_raw, inspect_workspace
+    from transplat_b200.synthetic import make_scene
+    sc = make_scene(n_views=7, seed=77, render_hw=(2048, 2048))
     dev = "cuda"
-    V = sc.extrinsics.shape[0]
     cams = pack_cameras_device(sc.extrinsics.to(dev), sc.intrinsics.to(dev), sc.near.to(dev), sc.far.to(dev),
                                torch.zeros(3, device=dev))
-    cfg = RenderConfig(H=1024, W=1024, V=V, sh_degree=4, sh_layout=SH_G3M, cov_layout=COV_FULL9, depth_mode=1)
-    return (sc.means[None].to(dev), sc.covariances[None].to(dev), sc.harmonics[None].to(dev), sc.opacities[None].to(dev),
-            cams, cfg)
+    ins = {}
+    for sort in ("bucket", "onesweep"):
+        cfg = RenderConfig(H=2048, W=2048, V=7, sh_degree=4, sh_layout=SH_G3M, cov_layout=COV_FULL9, depth_mode=1,
+                           sort=sort, check="sync")
+        color, depth, _, state = forward_raw(cfg, sc.means[None].to(dev), sc.covariances[None].to(dev),
+                                             sc.harmonics[None].to(dev), sc.opacities[None].to(dev), cams)
+        w = inspect_workspace(state)
+        assert w["overflow"] == 0 and w["num_rendered"] == int(w["tiles_touched"].sum())
+        ins[sort] = (w["keys"].clone(), w["vals"].clone(), w["ranges"].clone(), color, depth)
+        del state, w
+    a, b = ins["bucket"], ins["onesweep"]
+    assert torch.equal(a[0], b[0]) and torch.equal(a[1], b[1])
+    ne = a[2][..., 1] > a[2][..., 0]
+    assert torch.equal(ne, b[2][..., 1] > b[2][..., 0]) and torch.equal(a[2][ne], b[2][ne])
+    lens = (a[2][..., 1] - a[2][..., 0]).sum()
+    assert int(lens) == a[0].numel()
+    assert float((a[3] - b[3]).abs().max()) <= 1e-6 and float((a[4] - b[4]).abs().max()) <= 1e-6
+
+
+def test_unmodified_reference_file_through_the_shim():
+    """The UNMODIFIED /root/reference/src/model/decoder/cuda_splatting.py imported with this repository's
+    `diff_gaussian_rasterization` package standing in for the extension: render_cuda / render_depth_cuda of the
+    reference file itself drive libtsplat.so, and the images equal the golden fixture (made by the same file with the
+    CPU oracle underneath) and the batched level-2 decoder.  Needs the reference tree (absent on the GPU box: skipped
+    there; the CPU twin tests/test_cpu_host.py::test_unmodified_reference_file_marshals_like_the_batched_path runs
+    everywhere the tree exists)."""
+    ref_root = os.environ.get("TSPLAT_REFERENCE_ROOT", "/root/reference")
+    if not os.path.exists(os.path.join(ref_root, "src", "model", "decoder", "cuda_splatting.py")):
+        pytest.skip("reference tree not present on this machine")
+    import diff_gaussian_rasterization as shim
+    from oracle.rasterizer_cpu import load_reference_cuda_splatting
+    ref = load_reference_cuda_splatting(shim, ref_root)
+    z, t = _gold()
+    H, W = z["color"].shape[-2:]
+    V = z["extrinsics"].shape[0]
+    rep = lambda k: t(k)[None].expand(V, *z[k].shape)
+    leaves = [t(k).clone().requires_grad_(True) for k in ("means", "cov", "harmonics", "opacities")]
+    repl = lambda x: x[None].expand(V, *x.shape)
+    color = ref.render_cuda(t("extrinsics"), t("intrinsics"), t("near"), t("far"), (H, W), t("bg")[None].expand(V, 3),
+                            repl(leaves[0]), repl(leaves[1]), repl(leaves[2]), repl(leaves[3]))
+    assert np.abs(color.detach().cpu().numpy() - z["color"]).max() <= COLOR_ATOL
+    (color * t("w_color")).sum().backward()
+    for leaf, k in zip(leaves, ("g_means", "g_cov", "g_sh", "g_op")):
+        assert np.abs(leaf.grad.cpu().numpy() - z[k]).max() <= GRAD_RTOL * np.abs(z[k]).max(), k
+    for mode in ("depth", "disparity", "relative_disparity", "log"):
+        depth = ref.render_depth_cuda(t("extrinsics"), t("intrinsics"), t("near"), t("far"), (H, W), rep("means"),
+                                      rep("cov"), rep("opacities"), mode=mode)
+        assert np.abs(depth.cpu().numpy() - z[f"depth_{mode}"]).max() <= COLOR_ATOL, mode
+
+
+def test_scales_rotations_input_mode():
+    """GaussianRasterizer.forward(scales=, rotations=): computeCov3D of the extension (quaternion used as given, r x y z
+    order, NOT normalised) - the same image and gradients as passing the resulting covariance as cov3D_precomp, and
+    gradients w.r.t. scales / rotations against float64 autograd of the closed form."""
+    from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianRasterizer
+    means, cov, sh, op, cams, cfg = case("tiny_l1")
+    cam = cams[0].cuda()
+    G = means.shape[1]
+    g = torch.Generator().manual_seed(5)
+    scales = (0.05 + 0.2 * torch.rand(G, 3, generator=g)).cuda()
+    rot = torch.randn(G, 4, generator=g).cuda() * 0.8   # deliberately not unit length
+    mod = 1.3
+    s = GaussianRasterizationSettings(cfg.H, cfg.W, float(cam[35]), float(cam[36]), cam[37:40], mod,
+                                      cam[0:16].reshape(4, 4), cam[16:32].reshape(4, 4), cfg.sh_degree, cam[32:35], False, False)
+    m = (means[0] * float(cam[40])).cuda()
+    w = torch.randn(3, cfg.H, cfg.W, generator=g).cuda()
+
+    def cov_closed_form(sc, q):  # float64, written from the definition
+        r, x, y, zq = q.double().unbind(-1)
+        R = torch.stack((1 - 2 * (y * y + zq * zq), 2 * (x * y - r * zq), 2 * (x * zq + r * y),
+                         2 * (x * y + r * zq), 1 - 2 * (x * x + zq * zq), 2 * (y * zq - r * x),
+                         2 * (x * zq - r * y), 2 * (y * zq + r * x), 1 - 2 * (x * x + y * y)), -1).reshape(-1, 3, 3)
+        M = R * (sc.double() * mod)[:, None, :]
+        S = M @ M.transpose(1, 2)
+        return torch.stack((S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]), -1)
+
+    sc1, q1 = scales.clone().requires_grad_(True), rot.clone().requires_grad_(True)
+    img1, radii1 = GaussianRasterizer(s)(means3D=m, means2D=None, shs=sh[0].cuda(), opacities=op[0].cuda()[:, None],
+                                         scales=sc1, rotations=q1)
+    (img1 * w).sum().backward()
+    sc2, q2 = scales.clone().requires_grad_(True), rot.clone().requires_grad_(True)
+    cov6 = cov_closed_form(sc2, q2)
+    c32 = cov6.float().detach().requires_grad_(True)
+    img2, radii2 = GaussianRasterizer(s)(means3D=m, means2D=None, shs=sh[0].cuda(), opacities=op[0].cuda()[:, None],
+                                         cov3D_precomp=c32)
+    (img2 * w).sum().backward()
+    assert torch.equal(radii1, radii2)
+    assert float((img1 - img2).abs().max()) <= COLOR_ATOL
+    cov6.backward(c32.grad.double())
+    for a, b, name in ((sc1.grad, sc2.grad, "scales"), (q1.grad, q2.grad, "rotations")):
+        assert float((a - b).abs().max()) <= GRAD_RTOL * float(b.abs().max()), name
 
 
 def _gold():
@@ -527,3 +617,29 @@ def test_debug_flag_level1():
         outs.append((img.detach(), radii, m.grad))
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
     assert float((outs[0][2] - outs[1][2]).abs().max()) <= 1e-5 * float(outs[0][2].abs().max())
+
+
+def test_no_status_block_is_dropped_unread():
+    """A forward-only loop whose host runs ahead of the device (check='deferred': no wait anywhere): an overflowed call
+    in the middle must still surface - at a later call - and must have raised the capacity of its shape."""
+    from transplat_b200 import rasterize as rz
+    means, cov, sh, op, cams, cfg = case("mid_l2")
+    args = [x.cuda() for x in (means, cov, sh, op, cams)]
+    rz._capacity.sweep(wait=True)
+    key = (0, cams.shape[0], means.shape[1], cfg.H, cfg.W)
+    rz._capacity.cap[key] = 3000            # far too small for this scene
+    rz._capacity.calibrated.add(key)
+    cfg.check = "deferred"
+    with pytest.raises(rz.OverflowError_):
+        for _ in range(4):                  # nothing waits; every call queues its status block
+            rz.forward_raw(cfg, *args)
+        torch.cuda.synchronize()
+        rz.forward_raw(cfg, *args)          # at the latest the sweep at the start of this call reads the queued blocks
+    try:
+        rz._capacity.sweep(wait=True)       # the other truncated calls of the loop
+    except rz.OverflowError_:
+        pass
+    assert rz._capacity.cap[key] > 100_000  # grown from the observed pair count
+    *_, state = rz.forward_raw(cfg, *args)
+    assert rz.read_status(state).overflow == 0
+    rz._capacity.sweep(wait=True)

@@ -359,6 +359,30 @@ int tsplat_mark_visible(int32_t G, const float* means, const float* viewmatrix, 
   return TSPLAT_OK;
 }
 
+int tsplat_cov3d_forward(int32_t G, const float* scales, const float* rotations, float scale_modifier, float* cov6,
+                         void* cuda_stream) {
+  if (G < 0 || !scales || !rotations || !cov6 || (reinterpret_cast<uintptr_t>(rotations) & 15u)) {
+    set_error("bad cov3d_forward arguments (rotations must be 16-B aligned)");
+    return TSPLAT_EINVAL;
+  }
+  cudaError_t e = launch_cov3d_forward(G, scales, rotations, scale_modifier, cov6, static_cast<cudaStream_t>(cuda_stream));
+  if (e != cudaSuccess) return cuda_fail("cov3d_forward", e);
+  return TSPLAT_OK;
+}
+
+int tsplat_cov3d_backward(int32_t G, const float* scales, const float* rotations, float scale_modifier,
+                          const float* dL_dcov6, float* dL_dscales, float* dL_drotations, void* cuda_stream) {
+  if (G < 0 || !scales || !rotations || !dL_dcov6 || !dL_dscales || !dL_drotations ||
+      (reinterpret_cast<uintptr_t>(rotations) & 15u) || (reinterpret_cast<uintptr_t>(dL_drotations) & 15u)) {
+    set_error("bad cov3d_backward arguments (rotations and dL_drotations must be 16-B aligned)");
+    return TSPLAT_EINVAL;
+  }
+  cudaError_t e = launch_cov3d_backward(G, scales, rotations, scale_modifier, dL_dcov6, dL_dscales, dL_drotations,
+                                        static_cast<cudaStream_t>(cuda_stream));
+  if (e != cudaSuccess) return cuda_fail("cov3d_backward", e);
+  return TSPLAT_OK;
+}
+
 int tsplat_pack_cameras(int32_t N, const float* extrinsics, const float* intrinsics, const float* near_plane,
                         const float* far_plane, const float* bg, int32_t bg_stride, int32_t scale_invariant,
                         TsplatCamera* cams, void* cuda_stream) {

@@ -119,6 +119,9 @@ cudaError_t launch_adapter_forward(const TsplatAdapterProblem& p, float* means, 
 cudaError_t launch_adapter_backward(const TsplatAdapterProblem& p, const float* g_means, const float* g_cov,
                                     const float* g_harm, float* g_coords, float* g_depths, float* g_raw,
                                     cudaStream_t st, int* bad);
+cudaError_t launch_cov3d_forward(int G, const float* scales, const float* rot, float mod, float* cov6, cudaStream_t st);
+cudaError_t launch_cov3d_backward(int G, const float* scales, const float* rot, float mod, const float* dL_dcov6,
+                                  float* dL_dscales, float* dL_drot, cudaStream_t st);
 void launch_status_store(const void* workspace, void* host_alias, cudaStream_t st);
 cudaError_t launch_mark_visible(int G, const float* means, const float* view, uint8_t* present,
                                 cudaStream_t st);

@@ -33,51 +33,51 @@ class OverflowError_(RuntimeError):
 
 
 class _Capacity:
-    """d_cap per problem shape.  The pair count D is only known on the device; every call copies
-    it back asynchronously and the NEXT call of the same shape grows the capacity if needed."""
+    """d_cap per problem shape.  The pair count D is only known on the device; every call copies its status block back
+    asynchronously and EVERY status is eventually read: a later call of any shape sweeps the completed ones, grows
+    the capacity of their shape if needed and raises if one of them had overflowed (its images and gradients were
+    incomplete).  Nothing is dropped unread: a forward-only loop whose host runs ahead keeps its statuses queued
+    (bounded: beyond ``max_inflight`` the oldest one is waited for)."""
+
+    max_inflight = 64
 
     def __init__(self):
         self.cap = {}
-        self.pending = {}
+        self.inflight = []       # (key, pinned host block, event, d_cap, adaptive) of calls whose status has not been read
         self.calibrated = set()  # keys whose pair count has been observed at least once
-        self.unchecked = []  # (host, event, d_cap) of backward calls launched before their status arrived
         self.last_num_rendered = None  # pair count of the most recent call whose status has been read
 
-    def check_unchecked(self):
-        """Raise for an earlier call whose overflow flag could not be read without stalling."""
-        keep = []
-        bad = None
-        for host, event, d_cap in self.unchecked:
-            if not event.query():
-                keep.append((host, event, d_cap))
+    def sweep(self, wait: bool = False):
+        """Read every status block that has arrived (all of them with ``wait``); raise for an overflowed call."""
+        keep, bad = [], None
+        for i, (key, host, event, d_cap, adaptive) in enumerate(self.inflight):
+            overdue = len(self.inflight) - i > self.max_inflight
+            if not (wait or overdue or event.query()):
+                keep.append((key, host, event, d_cap, adaptive))
                 continue
+            event.synchronize()
             st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
+            if adaptive:
+                self.observe(key, st.num_rendered)
+            else:
+                self.last_num_rendered = int(st.num_rendered)
             if st.overflow:
-                bad = (st.num_rendered, d_cap)
-        self.unchecked = keep
+                bad = (int(st.num_rendered), d_cap)
+        self.inflight = keep
         if bad is not None:
             raise OverflowError_(
                 f"pair list overflow in an EARLIER render call: D={bad[0]} > d_cap={bad[1]}; its images and "
-                "gradients were incomplete.  Raise TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
+                "gradients were incomplete (the capacity has been raised for the next call).  Raise "
+                "TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
+
+    def forget(self, event):
+        """The caller has read this call's status itself."""
+        self.inflight = [e for e in self.inflight if e[2] is not event]
 
     def get(self, key, n_items):
-        self.poll(key)
         if key not in self.cap:
             self.cap[key] = min(max(int(_DEFAULT_PAIRS_PER_GAUSSIAN * n_items), 4096), (1 << 30) - 1)
         return self.cap[key]
-
-    def poll(self, key, wait=False):
-        p = self.pending.get(key)
-        if p is None:
-            return None
-        host, event = p
-        if not wait and not event.query():
-            return None
-        event.synchronize()
-        del self.pending[key]
-        st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
-        self.observe(key, st.num_rendered)
-        return st
 
     def observe(self, key, num_rendered):
         """Keep the capacity at >= 2x the last observed pair count (never shrinks)."""
@@ -183,8 +183,8 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
             raise RuntimeError("CUDA-graph capture needs a calibrated pair-list capacity: run one eager call of this "
                                "problem shape first (or pass RenderConfig.d_cap)")
         check = "graph"
-    elif _capacity.unchecked:
-        _capacity.check_unchecked()
+    else:
+        _capacity.sweep()  # statuses of earlier calls that have arrived: grow capacities, raise for an overflow
     with torch.cuda.device(dev):
         stream = torch.cuda.current_stream(dev)
         while True:
@@ -235,7 +235,7 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
                     _capacity.grow(key, st.num_rendered)
                     continue
             else:
-                _capacity.pending[key] = (host, event)
+                _capacity.inflight.append((key, host, event, d_cap, not cfg.d_cap))
             break
     state = _State()
     state.problem, state.workspace, state.d_cap, state.layout, state.key = prob, ws, d_cap, layout, key
@@ -266,21 +266,18 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
     means, cov, sh, opacity, cams = state.tensors
     if state.event is None or torch.cuda.is_current_stream_capturing():
         pass  # CUDA-graph capture: the caller checks read_status_device(state) after a replay
-    elif _capacity.unchecked:
-        _capacity.check_unchecked()
-    if state.event is None or torch.cuda.is_current_stream_capturing():
-        pass
     elif state.event.query() or (cfg.check or _CHECK_MODE) == "sync":
         st = read_status(state)
+        _capacity.forget(state.event)
+        if not cfg.d_cap:
+            _capacity.observe(state.key, st.num_rendered)
         if st.overflow:
             raise OverflowError_(
                 f"pair list overflow in the forward pass: D={st.num_rendered} > d_cap={state.d_cap}; the rendered "
                 "images were incomplete.  Raise TSPLAT_PAIRS_PER_GAUSSIAN or run with TSPLAT_CHECK=sync.")
-    else:
-        # the forward is still in flight (training step: backward is issued right behind it).  Do not
-        # stall the host: enqueue the backward now (memory-safe even after an overflow) and read the flag
-        # at the next call.
-        _capacity.unchecked.append((state.status_host, state.event, state.d_cap))
+    # else: the forward is still in flight (training step: backward is issued right behind it).  Do not stall the
+    # host: enqueue the backward now (memory-safe even after an overflow); the forward's status block stays queued
+    # in _capacity.inflight and the next call of any shape reads it and raises.
     dev = means.device
     N = means.shape[0] * cfg.V
     with torch.cuda.device(dev):

@@ -91,14 +91,41 @@ class GaussianRasterizer(nn.Module):
         return color[0], radii[0]
 
 
+class _Cov3D(torch.autograd.Function):
+    """computeCov3D of the extension (the scales / rotations input mode; unused by TranSplat) and its backward, one
+    kernel each (csrc/cov3d.cu): Sigma = R diag(s^2) R^T, s = scale_modifier * scale, quaternion (r, x, y, z) used as
+    given - the extension does not normalise it - upper triangle."""
+
+    @staticmethod
+    def forward(ctx, scales, rotations, mod):
+        if not scales.is_cuda:
+            raise RuntimeError("transplat_b200 renders on a CUDA device only (no CPU fallback)")
+        scales, rotations = scales.contiguous().float(), rotations.contiguous().float()
+        G = scales.shape[0]
+        cov6 = torch.empty((G, 6), dtype=torch.float32, device=scales.device)
+        with torch.cuda.device(scales.device):
+            st = torch.cuda.current_stream(scales.device).cuda_stream
+            _lib.check(_lib.lib().tsplat_cov3d_forward(G, scales.data_ptr(), rotations.data_ptr(), float(mod),
+                                                       cov6.data_ptr(), C.c_void_p(st)), "tsplat_cov3d_forward")
+        ctx.save_for_backward(scales, rotations)
+        ctx.mod = float(mod)
+        return cov6
+
+    @staticmethod
+    def backward(ctx, g_cov6):
+        scales, rotations = ctx.saved_tensors
+        G = scales.shape[0]
+        g_cov6 = g_cov6.contiguous().float()
+        g_s, g_q = torch.empty_like(scales), torch.empty_like(rotations)
+        with torch.cuda.device(scales.device):
+            st = torch.cuda.current_stream(scales.device).cuda_stream
+            _lib.check(_lib.lib().tsplat_cov3d_backward(G, scales.data_ptr(), rotations.data_ptr(), ctx.mod,
+                                                        g_cov6.data_ptr(), g_s.data_ptr(), g_q.data_ptr(),
+                                                        C.c_void_p(st)), "tsplat_cov3d_backward")
+        return g_s, g_q, None
+
+
 def _cov3d_from_scale_rotation(scales, rotations, mod):
-    """computeCov3D of the extension (the scales/rotations input mode; unused by TranSplat):
-    Sigma = R S S^T R^T with quaternion (r, x, y, z), upper triangle."""
-    q = rotations / rotations.norm(dim=-1, keepdim=True)
-    r, x, y, z = q.unbind(-1)
-    R = torch.stack((1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
-                     2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
-                     2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)), -1).reshape(-1, 3, 3)
-    Mx = R * (scales * mod)[:, None, :]
-    S = Mx @ Mx.transpose(1, 2)
-    return torch.stack((S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]), -1)
+    if scales.dim() != 2 or scales.shape[1] != 3 or rotations.dim() != 2 or rotations.shape[1] != 4:
+        raise RuntimeError("scales must have dimensions (num_points, 3) and rotations (num_points, 4)")
+    return _Cov3D.apply(scales, rotations, float(mod))
