@@ -204,6 +204,27 @@ def forward(scene: Scene, cam: np.ndarray, H: int, W: int, depth_mode=None, rend
     return st
 
 
+def borderline_pixels(st: ViewState, eps: float = 4e-7) -> np.ndarray:
+    """bool [H,W]: pixels of this view whose result hangs on a float comparison within rounding distance of its
+    threshold (alpha vs 1/255, T(1-alpha) vs 1e-4, power vs 0) - see oracle_render_borderline."""
+    flag = np.zeros((st.H, st.W), np.uint8)
+    lib().oracle_render_borderline(st.H, st.W, _p(st.ranges), _p(st.extra["vals_buf"]), _p(st.xy), _p(st.conic_opacity),
+                                   C.c_float(eps), _p(flag))
+    return flag.astype(bool)
+
+
+def gaussians_of_pixels(st: ViewState, mask: np.ndarray) -> np.ndarray:
+    """bool [G]: every Gaussian in the tile list of a pixel of ``mask``, up to that pixel's last contributor + 1
+    (the entry whose decision may have flipped can be the one right behind the recorded last contributor)."""
+    out = np.zeros(st.G, bool)
+    gx = (st.W + 15) // 16
+    for y, x in np.argwhere(mask):
+        t = (y // 16) * gx + (x // 16)
+        lo, hi = int(st.ranges[t, 0]), int(st.ranges[t, 1])
+        out[st.vals[lo:hi]] = True
+    return out
+
+
 class GradAccum:
     """binary64 accumulators for one scene; several views add into the same object."""
 

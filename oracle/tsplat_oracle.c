@@ -471,6 +471,52 @@ void oracle_render_forward(int H, int W, int CH, const uint32_t* ranges, const u
   }
 }
 
+/* Pixels whose result hangs on a float comparison that sits within rounding distance of its threshold: the same walk
+ * as oracle_render_forward, flag[pix] = 1 if for some evaluated entry
+ *   power is within eps of 0 (relative to its terms), or alpha within eps of 1/255, or T (1 - alpha) within eps of 1e-4.
+ * On such a pixel an implementation whose exp() differs in the last ulps (device ex2-based exp vs glibc expf) may
+ * legitimately take the other branch: one contribution of alpha ~ 1/255 more or less.  The parity tests hold every
+ * other pixel to the stated tolerance and these to a looser, explicit one (tests/parity.py). */
+void oracle_render_borderline(int H, int W, const uint32_t* ranges, const uint32_t* vals, const float* xy,
+                              const float* conic_opacity, float eps, uint8_t* flag) {
+  const int gx = (W + BLOCK - 1) / BLOCK, gy = (H + BLOCK - 1) / BLOCK;
+#pragma omp parallel for schedule(dynamic, 1)
+  for (int tile = 0; tile < gx * gy; tile++) {
+    const int tx = tile % gx, ty = tile / gx;
+    const uint32_t r0 = ranges[2 * tile], r1 = ranges[2 * tile + 1];
+    for (int ly = 0; ly < BLOCK; ly++)
+      for (int lx = 0; lx < BLOCK; lx++) {
+        const int px = tx * BLOCK + lx, py = ty * BLOCK + ly;
+        if (px >= W || py >= H) continue;
+        const float pxf = (float)px, pyf = (float)py;
+        float T = 1.0f;
+        uint8_t f = 0;
+        for (uint32_t e = r0; e < r1; e++) {
+          const uint32_t g = vals[e];
+          const float dx = xy[2 * g] - pxf, dy = xy[2 * g + 1] - pyf;
+          const float* co = conic_opacity + 4 * (size_t)g;
+          const float power = -0.5f * (co[0] * dx * dx + co[2] * dy * dy) - co[1] * dx * dy;
+          const float mag = 0.5f * (fabsf(co[0]) * dx * dx + fabsf(co[2]) * dy * dy) + fabsf(co[1] * dx * dy);
+          if (fabsf(power) <= eps * mag && co[3] >= 1.0f / 255.0f) f = 1;
+          if (power > 0.0f) continue;
+          const float alpha = fminf(0.99f, co[3] * expf(power));
+          /* two exp implementations, each within ~2 ulp, plus the rounding of the argument (an absolute error
+           * ~6e-8 |power| in the exponent is a relative one in exp) and of o * exp: eps (1 + 0.3 |power|), eps = 4e-7 */
+          const float rel = eps * (1.0f + 0.3f * fabsf(power));
+          if (fabsf(alpha - 1.0f / 255.0f) <= rel * (1.0f / 255.0f)) f = 1;
+          if (alpha < 1.0f / 255.0f) continue;
+          const float test_T = T * (1.0f - alpha);
+          /* T is a product of up to hundreds of factors (1 - alpha_i), each off by alpha_i rel / (1 - alpha_i):
+           * with sum(alpha_i) ~ ln(1e4) at the threshold the products differ by up to ~50 eps */
+          if (fabsf(test_T - 0.0001f) <= 50.0f * eps * 0.0001f) f = 1;
+          if (test_T < 0.0001f) break;
+          T = test_T;
+        }
+        flag[(size_t)py * W + px] = f;
+      }
+  }
+}
+
 /* --------------------------------------------------------------- backward ------ */
 
 /* renderCUDA backward (X9).  Per-pixel arithmetic in binary32 as the reference; the per-Gaussian

@@ -253,6 +253,7 @@ def read_status(state) -> TsplatStatus:
     if state.event is None:  # captured in a CUDA graph: read the device copy
         return read_status_device(state)
     state.event.synchronize()
+    _capacity.forget(state.event)  # the caller has the flag now: a later call's sweep need not raise for it again
     return TsplatStatus.from_buffer_copy(state.status_host.numpy().tobytes())
 
 
