@@ -23,7 +23,9 @@
  *   - the size of the tile/Gaussian pair list ("num_rendered", D) is not known on the host:
  *     the caller supplies a capacity d_cap; if D > d_cap the status block's `overflow` flag is
  *     set, pairs beyond the capacity are dropped, and the caller retries with a larger
- *     workspace (tsplat_status_read tells it how large).
+ *     workspace (tsplat_status_read tells it how large).  A forward whose lists overflowed also
+ *     POISONS its outputs on the device (NaN in the first colour value and in the fused loss), so a
+ *     training loop cannot consume a truncated step unnoticed.
  */
 #ifndef TSPLAT_H_
 #define TSPLAT_H_
@@ -35,7 +37,7 @@
 extern "C" {
 #endif
 
-#define TSPLAT_VERSION 100
+#define TSPLAT_VERSION 200
 
 /* error codes */
 #define TSPLAT_OK 0
@@ -154,14 +156,25 @@ typedef struct TsplatLayout {
   int32_t sort_passes;
   int32_t rec_stride;     /* byte stride of the interleaved xy / conic_opacity / rgbd sections    */
   int32_t reserved0;
+  /* per-8x4-block lists (what the render kernels stream; see TsplatStatus.num_block_entries) */
+  uint64_t block_jobs;    /* uint4 [N*T*8]  one render job per (view, tile, block), tiles in heaviest-first order:
+                             first reference, reference count, (view*T + tile)*8 + block, 0            */
+  uint64_t block_refs;    /* uint2 [e_cap]: Gaussian id, 1-based position in the TILE list; a block's references
+                             are contiguous and in list order                                          */
+  uint64_t e_cap;         /* capacity of block_refs in entries (TSPLAT_BLOCK_ENTRY_RATIO * d_cap)     */
 } TsplatLayout;
 
 /* Device-side status block (first bytes of the workspace). */
 typedef struct TsplatStatus {
   uint64_t num_rendered; /* D over all views of the call (may exceed d_cap when overflow != 0)    */
-  uint32_t overflow;     /* 1 if D > d_cap                                                        */
+  uint32_t overflow;     /* 1 if D > d_cap or E > TSPLAT_BLOCK_ENTRY_RATIO * d_cap                 */
   uint32_t reserved;
+  uint64_t num_block_entries; /* E: entries of the per-8x4-block lists the render kernels stream (each pair is
+                                 listed once per pixel block of its tile it can touch: 1.1-1.3 D for encoder-sized
+                                 Gaussians, up to 8 D for tile-covering ones); capacity = TSPLAT_BLOCK_ENTRY_RATIO * d_cap */
+  uint64_t reserved1;
 } TsplatStatus;
+#define TSPLAT_BLOCK_ENTRY_RATIO 2
 
 int tsplat_version(void);
 const char* tsplat_last_error(void);
@@ -241,7 +254,7 @@ int tsplat_pack_cameras(int32_t N, const float* extrinsics, const float* intrins
                         void* cuda_stream);
 
 /* Copies the status block to host memory asynchronously on the stream.  status_host should be pinned
- * (cudaHostAlloc / cudaHostRegister, 16-byte aligned): it is then written by a one-warp kernel through its
+ * (cudaHostAlloc / cudaHostRegister, 16-byte aligned, 32 bytes): it is then written by a one-warp kernel through its
  * device alias, so the read never queues on a copy engine behind another stream's bulk transfer; pageable
  * memory falls back to cudaMemcpyAsync. */
 int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* cuda_stream);

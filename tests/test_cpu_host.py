@@ -26,7 +26,7 @@ def test_library_exports_every_declared_symbol():
     L = _lib.lib()
     for name in declared:
         assert hasattr(L, name), name
-    assert L.tsplat_version() == 100
+    assert L.tsplat_version() == 200
 
 
 def _problem(B=1, G=131072, V=4, H=256, W=256):

@@ -38,7 +38,8 @@ class TsplatLayout(C.Structure):
     _fields_ = [(n, C.c_uint64) for n in (
         "total_bytes", "status", "depths", "radii", "xy", "conic_opacity", "rgbd", "tiles_touched",
         "clamped", "keys", "vals", "ranges", "final_T", "n_contrib", "grad_acc")] + [
-        (n, C.c_int32) for n in ("tiles_x", "tiles_y", "sort_bits", "sort_passes", "rec_stride", "reserved0")]
+        (n, C.c_int32) for n in ("tiles_x", "tiles_y", "sort_bits", "sort_passes", "rec_stride", "reserved0")] + [
+        (n, C.c_uint64) for n in ("block_jobs", "block_refs", "e_cap")]
 
 
 class TsplatMse(C.Structure):
@@ -47,7 +48,11 @@ class TsplatMse(C.Structure):
 
 
 class TsplatStatus(C.Structure):
-    _fields_ = [("num_rendered", C.c_uint64), ("overflow", C.c_uint32), ("reserved", C.c_uint32)]
+    _fields_ = [("num_rendered", C.c_uint64), ("overflow", C.c_uint32), ("reserved", C.c_uint32),
+                ("num_block_entries", C.c_uint64), ("reserved1", C.c_uint64)]
+
+
+BLOCK_ENTRY_RATIO = 2  # TSPLAT_BLOCK_ENTRY_RATIO: capacity of the per-block lists = 2 * d_cap entries
 
 
 def build(verbose: bool = False) -> str:

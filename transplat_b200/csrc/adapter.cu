@@ -365,7 +365,7 @@ cudaError_t launch_adapter_forward(const TsplatAdapterProblem& p, float* means, 
   // a CTA's slab starts at (view*n + 128*k) rows: 16-B aligned iff every such offset is (row bytes * 128 always is)
   a.bulk_ok = al16(p.raw) && ((size_t)p.n * a.row * 4) % 16 == 0;
   const size_t smem = 1024 + sizeof(float) * kAdBlock * a.row;
-  cudaError_t e = cudaFuncSetAttribute(adapter_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(adapter_forward_kernel), (int)smem);
   if (e != cudaSuccess) return e;
   dim3 grid((p.n + kAdBlock - 1) / kAdBlock, p.N);
   adapter_forward_kernel<<<grid, kAdBlock, smem, st>>>(a);
@@ -381,7 +381,7 @@ cudaError_t launch_adapter_backward(const TsplatAdapterProblem& p, const float* 
   a.g_means = g_means; a.g_cov = g_cov; a.g_harm = g_harm; a.g_coords = g_coords; a.g_depths = g_depths; a.g_raw = g_raw;
   a.bulk_ok = al16(g_harm) && ((size_t)p.n * 3 * a.d_sh * 4) % 16 == 0;
   const size_t smem = 1024 + sizeof(float) * kAdBlock * (3 * a.d_sh + 7);
-  cudaError_t e = cudaFuncSetAttribute(adapter_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(adapter_backward_kernel), (int)smem);
   if (e != cudaSuccess) return e;
   dim3 grid((p.n + kAdBlock - 1) / kAdBlock, p.N);
   adapter_backward_kernel<<<grid, kAdBlock, smem, st>>>(a);

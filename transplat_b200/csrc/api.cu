@@ -5,9 +5,32 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
 
 namespace tsplat {
+
+cudaError_t ensure_dynamic_smem(const void* kernel, int bytes) {
+  struct Entry { int dev; const void* fn; int bytes; };
+  static std::mutex mu;
+  static std::vector<Entry> seen;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  std::lock_guard<std::mutex> lock(mu);
+  for (Entry& en : seen)
+    if (en.dev == dev && en.fn == kernel) {
+      if (bytes <= en.bytes) return cudaSuccess;
+      e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+      if (e == cudaSuccess) en.bytes = bytes;
+      return e;
+    }
+  e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  if (e == cudaSuccess) seen.push_back({dev, kernel, bytes});
+  return e;
+}
 
 static thread_local char g_err[512] = "";
 
@@ -69,7 +92,7 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   L.status = take(sizeof(Control));
   L.ranges = take(8ull * N * T);
   out->tile_cursor = take(4ull * N * T);
-  out->tile_last = take(4ull * N * T);
+  out->tile_jobs_done = take(4ull * N * T);
   // tile_count is accumulated by the preprocess kernel itself (bucket path), so that kernel cannot also be the one
   // that clears it: it sits last in the region and is cleared by a memset node ahead of the launch
   out->tile_count = take(4ull * N * T);
@@ -94,15 +117,22 @@ int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out) {
   const bool odd = L.sort_passes & 1;
   L.keys = odd ? k1 : k0; out->keys_alt = odd ? k0 : k1;
   L.vals = odd ? v1 : v0; out->vals_alt = odd ? v0 : v1;
-  out->rec0 = take(16 * d_cap);
-  out->rec1 = take(16 * d_cap);
-  out->rec2 = take(16 * d_cap);
+  // ---- per-block lists ----
+  out->e_cap = (uint64_t)kBlockEntryRatio * d_cap;
+  out->bref = take(8ull * (out->e_cap + 2));  // + the padding reference an odd last batch copies along
+  L.block_refs = out->bref; L.e_cap = out->e_cap;
+  out->pair_mask = take(d_cap);
+  out->block_jobs = take(16ull * kBlocksPerTile * N * T);
+  out->segs = take(16ull * (out->e_cap / kSegLen + kBlocksPerTile * N * T + 1));
+  out->ckpt = take(4ull * kCkptFloats * (out->e_cap / kSegLen + 2));
+  out->c_final = take(16ull * N * P);
+  L.block_jobs = out->block_jobs;
   // ---- per pixel ----
   L.final_T = take(4 * N * P);
   L.n_contrib = take(4 * N * P);
   // ---- backward ----
   L.grad_acc = take(4ull * kAccFloats * NG);
-  out->loss_partial = take(4ull * N * T * 2 * 2);  // loss and PSNR: one partial each per render-forward CTA (a tile may be split over 2)
+  out->loss_partial = take(4ull * N * T * 2 * (kBlocksPerTile + 1));  // loss and PSNR: one partial each per (tile, block) job and per tile
   L.total_bytes = off;
   return TSPLAT_OK;
 }
@@ -127,13 +157,18 @@ Workspace resolve(const LayoutFull& F, void* base, uint64_t d_cap, int N) {
   w.n_contrib = reinterpret_cast<unsigned int*>(b + L.n_contrib);
   w.grad_acc = reinterpret_cast<float*>(b + L.grad_acc);
   w.loss_partial = reinterpret_cast<float*>(b + F.loss_partial);
-  w.rec0 = reinterpret_cast<float4*>(b + F.rec0);
-  w.rec1 = reinterpret_cast<float4*>(b + F.rec1);
-  w.rec2 = reinterpret_cast<float4*>(b + F.rec2);
+  w.bref = reinterpret_cast<uint2*>(b + F.bref);
+  w.block_jobs = reinterpret_cast<uint4*>(b + F.block_jobs);
+  w.segs = reinterpret_cast<uint4*>(b + F.segs);
+  w.seg_cap = (unsigned int)(F.e_cap / kSegLen + (uint64_t)kBlocksPerTile * N * (L.tiles_x * L.tiles_y) + 1);
+  w.ckpt = reinterpret_cast<float*>(b + F.ckpt);
+  w.c_final = reinterpret_cast<float*>(b + F.c_final);
+  w.pair_mask = reinterpret_cast<unsigned char*>(b + F.pair_mask);
+  w.tile_jobs_done = reinterpret_cast<unsigned int*>(b + F.tile_jobs_done);
+  w.e_cap = F.e_cap;
   w.tile_order = reinterpret_cast<unsigned int*>(b + F.tile_order);
   w.tile_count = reinterpret_cast<unsigned int*>(b + F.tile_count);
   w.tile_cursor = reinterpret_cast<unsigned int*>(b + F.tile_cursor);
-  w.tile_last = reinterpret_cast<unsigned int*>(b + F.tile_last);
   w.big_list = reinterpret_cast<unsigned int*>(b + F.big_list);
   w.bucket = 1;
   w.use_order = (uint64_t)N * (uint64_t)(L.tiles_x * L.tiles_y) <= (uint64_t)kOrderMaxTiles ? 1 : 0;
@@ -239,6 +274,9 @@ static int forward_impl(const TsplatProblem* p, void* workspace, uint64_t worksp
     StageTimer t(kStZero, st);
     e = cudaMemsetAsync(static_cast<char*>(workspace) + F.zero_begin, 0, F.zero_end - F.zero_begin, st);
     if (e != cudaSuccess) return cuda_fail("memset(control)", e);
+    // every block list empty; the tile id of job j is j / 8 (identity order)
+    e = launch_empty_jobs(ws, st);
+    if (e != cudaSuccess) return cuda_fail("empty_jobs", e);
     ws.use_order = 0;
   } else {
     // the preprocess kernel also zeroes the control / cursors / ranges region (nothing in it is touched before the
@@ -262,13 +300,19 @@ static int forward_impl(const TsplatProblem* p, void* workspace, uint64_t worksp
       if (e != cudaSuccess) return cuda_fail("bucket_scan_emit", e);
       { StageTimer t(kStSort, st); e = debug_sync(p, st, launch_bucket_sort_gather(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("bucket_sort_gather", e);
+      { StageTimer t(kStRanges, st); e = debug_sync(p, st, launch_block_lists(*p, ws, st)); }
+      if (e != cudaSuccess) return cuda_fail("block_lists", e);
     } else {
       { StageTimer t(kStBin, st); e = debug_sync(p, st, launch_bin_emit(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("bin_emit", e);
       { StageTimer t(kStSort, st); e = debug_sync(p, st, launch_sort(*p, ws, st)); }
       if (e != cudaSuccess) return cuda_fail("sort", e);
-      { StageTimer t(kStRanges, st); e = debug_sync(p, st, launch_ranges_gather(*p, ws, st)); }
-      if (e != cudaSuccess) return cuda_fail("ranges_gather", e);
+      {
+        StageTimer t(kStRanges, st);
+        e = debug_sync(p, st, launch_ranges_gather(*p, ws, st));
+        if (e == cudaSuccess) e = debug_sync(p, st, launch_block_lists(*p, ws, st));
+      }
+      if (e != cudaSuccess) return cuda_fail("ranges / block_lists", e);
     }
   }
   { StageTimer t(kStRender, st); e = debug_sync(p, st, launch_render_forward(*p, ws, out_color, out_depth, mse, st)); }

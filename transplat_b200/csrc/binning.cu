@@ -326,8 +326,8 @@ __global__ void __launch_bounds__(kSortThreads) onesweep_pass_kernel(Workspace w
 }
 
 // ---------------------------------------------------------------------------------------------
-// 3. identifyTileRanges (X7) fused with the gather of per-entry records in sorted order, so the
-//    render kernels stream contiguous memory with TMA bulk copies instead of gathering by id.
+// 3. identifyTileRanges (X7) and the heaviest-first tile order; the per-block record lists the render kernels
+//    stream follow in block_lists_kernel (blocklist.cu), as in the bucket path.
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G) {
   const unsigned long long Dfull = ws.ctl->num_rendered;
@@ -342,17 +342,6 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
       if (tile != prev) { ws.ranges[prev].y = j; ws.ranges[tile].x = j; }
     }
     if (j == D - 1) ws.ranges[tile].y = D;
-    const unsigned int id = vals[j];
-    const size_t o = (size_t)(tile / (unsigned)ws.T) * G + id;
-    const float4* __restrict__ gr = ws.grec + o * 3;
-    const float4 g0 = gr[0], g1 = gr[1];
-    float4 g2 = gr[2];
-    // the per-Gaussian cull threshold becomes this pair's block mask (cull.cuh)
-    const unsigned int tl = tile % (unsigned)ws.T, ty = tl / (unsigned)ws.tiles_x, tx = tl - ty * (unsigned)ws.tiles_x;
-    g2.w = __uint_as_float(cull_block_mask(g0, g1.x, g2.w, (float)(tx * kTile), (float)(ty * kTile)));
-    ws.rec0[j] = g0;
-    ws.rec1[j] = g1;
-    ws.rec2[j] = g2;
   }
   if (!ws.use_order) return;
   // The last CTA to finish orders the (view, tile) ids by list length, longest first (counting sort

@@ -16,7 +16,7 @@
 //      writes keys and values in sorted order; tiles above kSmallTileCap go to a second launch
 //      (bitonic network in a 128-KB buffer), tiles above kBigTileCap are sorted in place in global
 //      memory by one CTA.
-//   5. gather_records_kernel: the 48-B per-Gaussian records copied into sorted order.
+//   5. block_lists_kernel (blocklist.cu, shared with the onesweep path): the per-8x4-block lists the render warps stream.
 //
 // Why: at C2 (1.6 M pairs, 42 key bits) six LSD passes were latency-bound at ~26 us each plus a
 // 38-us scan/emit and a 38-us range/gather pass (272 us before render); each pair now crosses HBM
@@ -230,7 +230,7 @@ __device__ __forceinline__ void bitonic_sort_words(unsigned long long* s, int n,
   }
 }
 
-// write keys / values of one sorted tile segment (the records follow in gather_records_kernel)
+// write keys / values of one sorted tile segment (the per-block record lists follow in block_lists_kernel)
 __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const unsigned long long* s, int n, unsigned int start,
                                                   int bid, int G, unsigned long long* __restrict__ keys_out,
                                                   unsigned int* __restrict__ vals_out, int tid, int nthreads) {
@@ -239,39 +239,6 @@ __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const uns
     const unsigned long long w = s[j];
     keys_out[start + j] = hiw | (w >> 32);
     vals_out[start + j] = (unsigned int)w;
-  }
-}
-
-// 5. gather of the 48-B per-Gaussian records (preprocess.cu) into sorted order: one thread per pair over the whole
-//    sorted list, full occupancy, coalesced 16-B stores to rec0/rec1/rec2 - what the render kernels stream with TMA.
-//    (Inside the per-tile sort CTAs - 2 per SM, load/sort/write phases serialised - the same copy took twice as long.)
-__global__ void __launch_bounds__(256) gather_records_kernel(Workspace ws, int G,
-                                                             const unsigned long long* __restrict__ keys,
-                                                             const unsigned int* __restrict__ vals) {
-  const unsigned long long Dfull = ws.ctl->num_rendered;
-  const unsigned int D = (unsigned int)(Dfull < ws.d_cap ? Dfull : ws.d_cap);
-  constexpr int U = 2;
-  const unsigned int stride = gridDim.x * blockDim.x;
-  for (unsigned int j0 = blockIdx.x * blockDim.x + threadIdx.x; j0 < D; j0 += U * stride) {
-    float4 q[U][3];
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const unsigned int j = j0 + u * stride;
-      if (j < D) {
-        const unsigned int bid = (unsigned int)(keys[j] >> 32);
-        const unsigned int view = bid / (unsigned)ws.T, tile = bid - view * (unsigned)ws.T;
-        const float4* __restrict__ gr = ws.grec + ((size_t)view * G + vals[j]) * 3;
-        q[u][0] = gr[0]; q[u][1] = gr[1]; q[u][2] = gr[2];
-        // the per-Gaussian cull threshold becomes this pair's block mask (cull.cuh)
-        const unsigned int ty = tile / (unsigned)ws.tiles_x, tx = tile - ty * (unsigned)ws.tiles_x;
-        q[u][2].w = __uint_as_float(cull_block_mask(q[u][0], q[u][1].x, q[u][2].w, (float)(tx * kTile), (float)(ty * kTile)));
-      }
-    }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      const unsigned int j = j0 + u * stride;
-      if (j < D) { ws.rec0[j] = q[u][0]; ws.rec1[j] = q[u][1]; ws.rec2[j] = q[u][2]; }
-    }
   }
 }
 
@@ -463,13 +430,7 @@ __global__ void __launch_bounds__(kTileSortThreads, 2) tile_sort_gather_kernel(W
   for (int i = tid; i < n; i += kTileSortThreads) s.words[i] = pairs[r.x + i];
   if (tid == 0) { s.dmin = 0xffffffffu; s.dmax = 0u; s.maxfill = 0u; }
   __syncthreads();
-#if defined(TSPLAT_EXP_RADIX_ONLY)
-  const bool sorted = false;
-#elif defined(TSPLAT_EXP_NOSORT)
-  const bool sorted = true;
-#else
   const bool sorted = distribution_sort_tile(s, n, tid);
-#endif
   if (!sorted) {  // clustered / equal depths: stable 8-bit LSD radix sort over the id digits, then the depth digits
     int id_passes = 1;
     while (id_passes < 4 && (G - 1) >> (8 * id_passes)) id_passes++;
@@ -526,19 +487,15 @@ cudaError_t launch_bucket_sort_gather(const TsplatProblem& p, const Workspace& w
   unsigned long long* keys_out = ws.keys[ws.sort_passes & 1];
   unsigned int* vals_out = ws.vals[ws.sort_passes & 1];
   const int NT = ws.N * ws.T;
-  cudaError_t e = cudaFuncSetAttribute(tile_sort_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)sizeof(TileSortSmem));
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(tile_sort_gather_kernel), (int)sizeof(TileSortSmem));
   if (e != cudaSuccess) return e;
   tile_sort_gather_kernel<<<NT, kTileSortThreads, sizeof(TileSortSmem), st>>>(ws, p.G, pairs, keys_out, vals_out);
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const int smem = kBigTileCap * (int)sizeof(unsigned long long);
-  e = cudaFuncSetAttribute(big_tile_sort_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  e = ensure_dynamic_smem(reinterpret_cast<const void*>(big_tile_sort_gather_kernel), smem);
   if (e != cudaSuccess) return e;
   big_tile_sort_gather_kernel<<<148, 512, smem, st>>>(ws, p.G, pairs, keys_out, vals_out);
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-  gather_records_kernel<<<148 * 8, 256, 0, st>>>(ws, p.G, keys_out, vals_out);
   return cudaGetLastError();
 }
 

@@ -177,8 +177,8 @@ cudaError_t launch_pack_cameras(int N, const float* extrinsics, const float* int
 
 // 16-byte status block -> pinned host memory through its device alias (tsplat_status_read)
 __global__ void status_store_kernel(const uint4* __restrict__ status, uint4* host_alias) {
-  if (threadIdx.x == 0) {
-    *host_alias = *status;
+  if (threadIdx.x < 2) {  // the 32-byte TsplatStatus
+    host_alias[threadIdx.x] = status[threadIdx.x];
     __threadfence_system();
   }
 }

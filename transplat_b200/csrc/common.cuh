@@ -31,7 +31,12 @@ constexpr int kSortTile = kSortThreads * kSortKpt;
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 constexpr int kMaxPasses = 8;
-constexpr int kBatch = 256;                 // list entries staged per TMA batch in the render kernels
+constexpr int kBlocksPerTile = 8;            // 8x4-pixel blocks of a 16x16 tile = warp jobs of the render kernels
+constexpr int kBlockEntryRatio = 2;          // capacity of the per-block lists in entries per pair-list slot (e_cap = 2 d_cap)
+constexpr int kRecFloat4 = 3;                // one per-Gaussian record = 3 x float4 = 48 B
+constexpr int kSegLen = 64;                  // render_backward work unit: references per list segment (a multiple of 32);
+                                             // render_forward leaves a per-pixel checkpoint at every multiple of it
+constexpr int kCkptFloats = 5 * 32;          // one checkpoint: T and the 4 channel prefixes of the block's 32 pixels
 constexpr int kSmallTileCap = 4096;          // bucket path: pairs per tile sorted by the small-tile kernel (32 KB smem)
 constexpr int kBigTileCap = 16384;           // ... by the big-tile kernel in shared memory (128 KB); beyond: in global memory
 constexpr int kOrderMaxTiles = 8192;         // order (view, tile) CTAs heaviest-first only up to this many
@@ -42,11 +47,15 @@ struct Control {
   unsigned long long num_rendered;  // D (uncapped)
   unsigned int overflow;
   unsigned int reserved;
+  unsigned long long num_block_entries;  // entries of all per-block lists (uncapped; block_lists_kernel's allocation cursor)
+  unsigned long long reserved1;          // (the first 32 bytes are the public TsplatStatus)
   unsigned int scan_tile_counter;   // dynamic tile ids for bin_emit
   unsigned int sort_tile_counter[kMaxPasses];
   unsigned int gather_done;         // CTAs of ranges_gather that have finished (last one orders the tiles)
   unsigned int num_big;             // bucket path: tiles whose list does not fit the small-tile sort kernel
-  unsigned int loss_done;           // CTAs of render_forward that have written their MSE partial (fused loss)
+  unsigned int loss_done;           // tiles of render_forward whose MSE partial is complete (fused loss)
+  unsigned int fwd_next;            // render_forward: jobs handed out beyond each warp's first one
+  unsigned int seg_full, seg_part;  // render_backward work units emitted by render_forward: full / partial list segments
   unsigned int hist[kMaxPasses][kRadix];  // global digit histograms (onesweep: one upfront sweep)
 };
 
@@ -65,14 +74,25 @@ struct Workspace {
   float* final_T;
   unsigned int* n_contrib;
   float* grad_acc;
-  float* loss_partial;             // fused MSE loss: one partial sum per (view, tile) CTA of render_forward
-  float4* rec0;  // x, y, conic.x, conic.y                      (sorted order)
-  float4* rec1;  // conic.z, opacity, r, g
-  float4* rec2;  // b, depth feature, bits(Gaussian id), cull threshold tau_s (cull.cuh)
+  float* loss_partial;             // fused MSE loss / PSNR partial sums: [2][N*T*8] per (tile, block) job, then [2][N*T] per tile
+  unsigned int* tile_jobs_done;    // per (view, tile): block jobs of render_forward that have written their loss partial
+  // per-block lists (blocklist.cu): the entries of a tile's sorted list that can touch one 8x4 pixel block, in list order,
+  // as references (Gaussian id, 1-based position in the TILE list) - contiguous per block: a render warp streams its
+  // own list with 1-D TMA bulk copies and gathers the 48-B records from grec
+  uint2* bref;
+  // render job records: first reference, reference count, (view*T + tile) * 8 + block, 0
+  uint4* block_jobs;               // in the order render_forward deals them: heaviest tile first (block_lists_kernel)
+  // render_backward work units (emitted by render_forward): a block list cut at its deepest contributor and then into
+  // segments of kSegLen references: first reference of the LIST, cut length, job id, segment index.  Full segments grow
+  // from the front of the table, partial ones from its back; dealt round-robin over the warps of the launch.
+  uint4* segs;
+  unsigned int seg_cap;
+  float* ckpt;                     // [e_cap / kSegLen + 2][5][32] per-pixel state in front of reference k * kSegLen of a list
+  float* c_final;                  // [N][4][H*W] the composited sums (colour without background, raw depth channel)
+  unsigned char* pair_mask;        // per sorted pair: its 8-bit block mask (cull.cuh), between the two passes of block_lists
+  unsigned long long e_cap;        // capacity of brec in entries
   unsigned int* tile_count;        // bucket path: pairs per (view, tile), counted by the preprocess kernel
   unsigned int* tile_cursor;       // bucket path: emission cursors per (view, tile)
-  unsigned int* tile_last;         // per (view, tile): 1 + list position of the deepest contributor of any pixel
-                                   // (render_forward, atomicMax); render_backward starts its walk there
   unsigned int* big_list;          // bucket path: (view, tile) ids with more than kSmallTileCap pairs
   int bucket;                      // 1: bucket path (count -> scan -> emit -> per-tile sort), 0: onesweep LSD path
   unsigned int* tile_order;        // (view, tile) ids, heaviest list first (render launch order)
@@ -87,10 +107,15 @@ struct Workspace {
 
 struct LayoutFull {
   TsplatLayout pub;
-  uint64_t keys_alt, vals_alt, rec0, rec1, rec2, loss_partial, scan_state, sort_state, tile_order, tile_count, tile_cursor, tile_last, big_list,
+  uint64_t keys_alt, vals_alt, bref, block_jobs, segs, ckpt, c_final, pair_mask, tile_jobs_done, loss_partial, scan_state, sort_state,
+      tile_order, tile_count, tile_cursor, big_list, e_cap,
       zero_begin, zero_mid, zero_end;  // [zero_begin, zero_mid) is all the bucket path needs cleared
   int num_scan_tiles, num_sort_tiles;
 };
+
+// Raises a kernel's dynamic shared-memory limit once per (device, kernel, size) instead of on every launch
+// (cudaFuncSetAttribute is a driver call; the attribute is per device).  Thread-safe.
+cudaError_t ensure_dynamic_smem(const void* kernel, int bytes);
 
 int compute_layout(const TsplatProblem& p, uint64_t d_cap, LayoutFull* out);
 Workspace resolve(const LayoutFull& L, void* base, uint64_t d_cap, int N);
@@ -104,6 +129,8 @@ cudaError_t launch_bucket_sort_gather(const TsplatProblem& p, const Workspace& w
 cudaError_t launch_bin_emit(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_sort(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
 cudaError_t launch_ranges_gather(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_block_lists(const TsplatProblem& p, const Workspace& ws, cudaStream_t st);
+cudaError_t launch_empty_jobs(const Workspace& ws, cudaStream_t st);  // G == 0: every render job has an empty list
 cudaError_t launch_render_forward(const TsplatProblem& p, const Workspace& ws, float* out_color,
                                   float* out_depth, const TsplatMse* mse, cudaStream_t st);
 cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, const float* dL_dcolor,

@@ -236,8 +236,7 @@ cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* 
   a.hist_views = ws.T <= kHistMaxBins ? (kHistMaxBins / ws.T < p.V ? kHistMaxBins / ws.T : p.V) : 0;
   const size_t smem = 16 + sizeof(float) * kPreBlock * (1 + 3 + a.cov_floats + a.sh_floats) +
                       (ws.bucket ? sizeof(unsigned int) * (size_t)a.hist_views * ws.T : 0);
-  cudaError_t e = cudaFuncSetAttribute(preprocess_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem);
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(preprocess_forward_kernel), (int)smem);
   if (e != cudaSuccess) return e;
   dim3 grid((p.G + kPreBlock - 1) / kPreBlock, p.B);
   preprocess_forward_kernel<<<grid, kPreBlock, smem, st>>>(a, ws, out_radii);

@@ -121,9 +121,6 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
       const float fx = (float)p.W / (2.0f * tanx), fy = (float)p.H / (2.0f * tany);
 
       // ---- cov2D backward (A.4) ----
-#ifdef TSPLAT_EXP_NOCOV
-      if (q0.x == 123.456f) continue;
-#endif
       Cov2D q;
       compute_cov2d(m, fx, fy, tanx, tany, c6, vm, q);
       const float aa = q.a, bb = q.b, cc = q.c;
@@ -187,11 +184,7 @@ __global__ void __launch_bounds__(kPreBwdBlock) preprocess_backward_kernel(PreBw
       dmean[2] += (pj[8] * m_w - pj[11] * mul1) * dmx + (pj[9] * m_w - pj[11] * mul2) * dmy;
 
       // ---- SH backward (A.5) ----
-#ifdef TSPLAT_EXP_NOSH
-      if (M > 0 && dcol[0] == 123.456f) {
-#else
       if (M > 0) {
-#endif
 #pragma unroll
         for (int ch = 0; ch < 3; ch++)
           if (cl & (1u << ch)) dcol[ch] = 0.0f;
@@ -279,8 +272,7 @@ cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& 
   a.dL_dmeans = dL_dmeans; a.dL_dcov = dL_dcov; a.dL_dsh = dL_dsh; a.dL_dopacity = dL_dopacity;
   a.dL_dmeans2D = dL_dmeans2D;
   const size_t smem = 16 + sizeof(float) * kPreBwdBlock * (3 + a.cov_floats + 2 * a.sh_floats);
-  cudaError_t e = cudaFuncSetAttribute(preprocess_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                       (int)smem);
+  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(preprocess_backward_kernel), (int)smem);
   if (e != cudaSuccess) return e;
   dim3 grid((g_count + kPreBwdBlock - 1) / kPreBwdBlock, p.B);
   preprocess_backward_kernel<<<grid, kPreBwdBlock, smem, st>>>(a, ws);

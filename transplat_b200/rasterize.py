@@ -46,6 +46,7 @@ class _Capacity:
         self.inflight = []       # (key, pinned host block, event, d_cap, adaptive) of calls whose status has not been read
         self.calibrated = set()  # keys whose pair count has been observed at least once
         self.last_num_rendered = None  # pair count of the most recent call whose status has been read
+        self.last_num_block_entries = None
 
     def sweep(self, wait: bool = False):
         """Read every status block that has arrived (all of them with ``wait``); raise for an overflowed call."""
@@ -58,7 +59,7 @@ class _Capacity:
             event.synchronize()
             st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
             if adaptive:
-                self.observe(key, st.num_rendered)
+                self.observe(key, st.num_rendered, st.num_block_entries)
             else:
                 self.last_num_rendered = int(st.num_rendered)
             if st.overflow:
@@ -79,11 +80,14 @@ class _Capacity:
             self.cap[key] = min(max(int(_DEFAULT_PAIRS_PER_GAUSSIAN * n_items), 4096), (1 << 30) - 1)
         return self.cap[key]
 
-    def observe(self, key, num_rendered):
-        """Keep the capacity at >= 2x the last observed pair count (never shrinks)."""
+    def observe(self, key, num_rendered, num_block_entries=0):
+        """Keep the capacity at >= 2x the last observed pair count D and the per-block lists' capacity
+        (BLOCK_ENTRY_RATIO x d_cap entries) at >= 2x the last observed entry count E (never shrinks)."""
         self.calibrated.add(key)
         self.last_num_rendered = int(num_rendered)
-        want = min(int(num_rendered * 2) + 4096, (1 << 30) - 1)
+        self.last_num_block_entries = int(num_block_entries)
+        want = max(int(num_rendered * 2), int(num_block_entries * 2) // _lib.BLOCK_ENTRY_RATIO + 1)
+        want = min(want + 4096, (1 << 30) - 1)
         if want > self.cap.get(key, 0):
             self.cap[key] = want
 
@@ -219,7 +223,7 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
             if capturing:
                 host = event = None
                 break
-            host = torch.empty(16, dtype=torch.uint8, pin_memory=True)
+            host = torch.empty(32, dtype=torch.uint8, pin_memory=True)
             _lib.check(L.tsplat_status_read(_ptr(ws), C.c_void_p(host.data_ptr()),
                                             C.c_void_p(stream.cuda_stream)), "tsplat_status_read")
             event = torch.cuda.Event()
@@ -228,11 +232,11 @@ def forward_raw(cfg: RenderConfig, means, cov, sh, opacity, cams, mse_target=Non
                 event.synchronize()
                 st = TsplatStatus.from_buffer_copy(host.numpy().tobytes())
                 if not cfg.d_cap:
-                    _capacity.observe(key, st.num_rendered)
+                    _capacity.observe(key, st.num_rendered, st.num_block_entries)
                 if st.overflow:
                     if cfg.d_cap:
-                        raise OverflowError_(f"pair list overflow: D={st.num_rendered} > d_cap={d_cap}")
-                    _capacity.grow(key, st.num_rendered)
+                        raise OverflowError_(f"pair list overflow: D={st.num_rendered} (block-list entries "
+                                             f"{st.num_block_entries}) > d_cap={d_cap}")
                     continue
             else:
                 _capacity.inflight.append((key, host, event, d_cap, not cfg.d_cap))
@@ -259,7 +263,7 @@ def read_status(state) -> TsplatStatus:
 
 def read_status_device(state) -> TsplatStatus:
     """Blocking read of the status block straight from the workspace (after a graph replay, or for debugging)."""
-    return TsplatStatus.from_buffer_copy(state.workspace[:16].cpu().numpy().tobytes())
+    return TsplatStatus.from_buffer_copy(state.workspace[:32].cpu().numpy().tobytes())
 
 
 def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=None):
@@ -271,7 +275,7 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
         st = read_status(state)
         _capacity.forget(state.event)
         if not cfg.d_cap:
-            _capacity.observe(state.key, st.num_rendered)
+            _capacity.observe(state.key, st.num_rendered, st.num_block_entries)
         if st.overflow:
             raise OverflowError_(
                 f"pair list overflow in the forward pass: D={st.num_rendered} > d_cap={state.d_cap}; the rendered "
@@ -467,6 +471,7 @@ def inspect_workspace(state) -> dict:
 
     return {
         "num_rendered": int(st.num_rendered), "overflow": int(st.overflow), "T": T,
+        "num_block_entries": int(st.num_block_entries),
         "sort_bits": lay.sort_bits,
         "depths": sec(lay.depths, 4 * N * G, torch.float32, (N, G)),
         "radii": sec(lay.radii, 4 * N * G, torch.int32, (N, G)),
@@ -482,4 +487,6 @@ def inspect_workspace(state) -> dict:
         "final_T": sec(lay.final_T, 4 * N * H * W, torch.float32, (N, H, W)),
         "n_contrib": sec(lay.n_contrib, 4 * N * H * W, torch.int32, (N, H, W)),
         "grad_acc": sec(lay.grad_acc, 48 * N * G, torch.float32, (N, G, 12)),
+        # per-block lists: jobs [N*T*8, 4] = first entry, count, (view*T + tile), 1 + deepest contributor's position
+        "block_jobs": sec(lay.block_jobs, 16 * N * T * 8, torch.int32, (N * T * 8, 4)),
     }
