@@ -648,3 +648,47 @@ def test_no_status_block_is_dropped_unread():
     *_, state = rz.forward_raw(cfg, *args)
     assert rz.read_status(state).overflow == 0
     rz._capacity.sweep(wait=True)
+
+
+def test_overflow_poisons_the_outputs_on_the_device():
+    """A call whose pair list (or block reference lists) exceeded the capacity is incomplete: besides the status flag, the
+    forward writes NaN into the first colour value and into the fused loss, so that a training loop - or a replayed CUDA
+    graph, where nothing is read back per step - cannot consume a truncated step unnoticed."""
+    from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
+    from transplat_b200.graphs import GraphedStep
+    from transplat_b200 import rasterize as rz
+    from transplat_b200.synthetic import make_scene
+    means, cov, sh, op, cams, cfg = case("mid_l2")
+    args = [x.cuda() for x in (means, cov, sh, op, cams)]
+    target = torch.rand(cams.shape[0], 3, cfg.H, cfg.W, device="cuda")
+    cfg.check, cfg.d_cap = "deferred", 5000
+    color, depth, _, state = rz.forward_raw(cfg, *args, mse_target=target)
+    st = rz.read_status(state)
+    assert st.overflow == 1
+    assert torch.isnan(color.flatten()[0]) and torch.isnan(state.mse[3]).all()
+    assert torch.isfinite(color.flatten()[1:]).all()
+    # graph replay: captured with a capacity calibrated on a sparse scene, replayed with covariances 400x larger
+    dec = DecoderSplattingCUDA().cuda()
+    sc = make_scene(n_ctx=1, h=48, w=48, n_views=2, seed=71, render_hw=(64, 64))
+    dev = lambda t: t[None].cuda()
+    static = [dev(t).clone() for t in (sc.means, sc.covariances, sc.harmonics, sc.opacities)]
+    cam = [dev(t) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
+    tgt = torch.rand(1, 2, 3, 64, 64, device="cuda")
+    one = torch.ones((), device="cuda")
+
+    def step():
+        leaves = [t.detach().requires_grad_(True) for t in static]
+        out, loss = dec.forward_mse(Gaussians(*leaves), *cam, (64, 64), tgt, depth_mode="depth")
+        g = torch.autograd.grad([loss], leaves, [one])
+        return out.color, loss, g, loss.grad_fn.state
+
+    gs = GraphedStep(step)
+    color, loss, g, state = gs.replay()
+    torch.cuda.synchronize()
+    assert torch.isfinite(loss) and rz.read_status_device(state).overflow == 0
+    with torch.no_grad():
+        static[1].mul_(400.0)
+    color, loss, g, state = gs.replay()
+    torch.cuda.synchronize()
+    assert rz.read_status_device(state).overflow == 1
+    assert not torch.isfinite(loss) and torch.isnan(color.flatten()[0])

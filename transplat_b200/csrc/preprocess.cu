@@ -2,101 +2,133 @@
 // launch, plus markVisible.  COMPILED WITH -fmad=false (see geom.cuh: the results feed the sort
 // keys, radii and tile rectangles, which must be bit-exact against the oracle).
 //
-// B200 design: one CTA = 128 Gaussians of one scene.  The CTA's slabs of the AoS inputs
-// (means 12 B, covariance 24/36 B, SH 300 B, opacity 4 B per Gaussian — contiguous per CTA) are
-// pulled into shared memory once with 1-D TMA bulk copies (cp.async.bulk, SASS UBLKCP) that
-// complete on an mbarrier, then every thread walks the V views reading its Gaussian from shared
-// memory (odd word strides: conflict-free) and writes the per-view SoA state coalesced.  SH is read
-// from HBM once per scene instead of once per view (the reference re-reads and re-copies it per
-// view: decoder_splatting_cuda.py:59-62, cuda_splatting.py:84).  HBM-bound: 340 B read once +
-// 53 B written per (view, Gaussian).
+// B200 design: one CTA = 32 Gaussians of one scene x all V views, one WARP per view (8 warps at most; more views are
+// walked in rounds).  The CTA's slabs of the AoS inputs (means 12 B, covariance 24/36 B, SH 300 B, opacity 4 B per
+// Gaussian - contiguous per CTA) are pulled into shared memory once with 1-D TMA bulk copies (cp.async.bulk, SASS
+// UBLKCP) that complete on an mbarrier; lane l of every warp then reads Gaussian l from shared memory (odd word
+// strides: conflict-free) and writes its view's SoA state coalesced.  SH is read from HBM once per scene instead of once
+// per view (the reference re-reads and re-copies it per view: decoder_splatting_cuda.py:59-62, cuda_splatting.py:84).
+// Round 1 walked the V views serially in one thread (128 Gaussians per CTA, 61 KB of shared memory, 12 warps per SM,
+// 1.06 TB/s of DRAM traffic): 11 KB per CTA and a thread per (Gaussian, view) keep 4x as many loads in flight.
+// HBM-bound: 340 B read once + 61 B written per (view, Gaussian).
 #include "cull.cuh"
 #include "geom.cuh"
 
 namespace tsplat {
+
+constexpr int kPreG = 32;          // Gaussians per CTA = lanes of a warp
+constexpr int kPreMaxWarps = 8;    // views handled concurrently by one CTA
+constexpr int kAggMaxArea = 16;    // tile rectangles up to this area are counted warp-aggregated
 
 struct PreArgs {
   TsplatProblem p;
   int cov_floats;  // 6 or 9
   int sh_floats;   // 3*M, or 3 for colors_precomp
   int bulk_ok;     // all slabs 16-B aligned
-  int hist_views;  // bucket path: views whose per-tile pair counters fit the shared-memory histogram (0: global reds)
   uint4* zero_ptr;              // control / look-back / ranges region to clear (replaces a memset launch)
   unsigned long long zero_vec;  // its size in 16-B words
 };
 
-__global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a, Workspace ws, int* out_radii) {
+// Pair counts per (view, tile) for the bucket path (blocklist / bucket.cu need them before any pair is emitted).  The 32
+// Gaussians of a warp are neighbours in a context image, so their tile rectangles overlap: the warp walks the union of
+// the small rectangles and adds ONE count per tile (ballot + popc) instead of one reduction per (Gaussian, tile) -
+// same-address global reductions serialise in L2.  Big rectangles are counted by their own lane.
+__device__ __forceinline__ void count_tiles(unsigned int* __restrict__ cnt, int gx, bool touched, int x0, int y0, int x1,
+                                            int y1, int lane) {
+  const int area = (x1 - x0) * (y1 - y0);
+  const bool small = touched && area <= kAggMaxArea;
+  if (touched && !small) {
+    for (int y = y0; y < y1; y++)
+      for (int x = x0; x < x1; x++) atomicAdd(cnt + y * gx + x, 1u);
+  }
+  if (__any_sync(0xffffffffu, small)) {
+    const int ux0 = __reduce_min_sync(0xffffffffu, small ? x0 : 0x7fffffff), uy0 = __reduce_min_sync(0xffffffffu, small ? y0 : 0x7fffffff);
+    const int ux1 = __reduce_max_sync(0xffffffffu, small ? x1 : 0), uy1 = __reduce_max_sync(0xffffffffu, small ? y1 : 0);
+    if ((ux1 - ux0) * (uy1 - uy0) <= 64) {
+      for (int y = uy0; y < uy1; y++)
+        for (int x = ux0; x < ux1; x++) {
+          const unsigned int m = __ballot_sync(0xffffffffu, small && x >= x0 && x < x1 && y >= y0 && y < y1);
+          if (lane == 0 && m) atomicAdd(cnt + y * gx + x, (unsigned int)__popc(m));
+        }
+    } else if (small) {  // Gaussians of this warp are scattered over the image (depth discontinuity): count one by one
+      for (int y = y0; y < y1; y++)
+        for (int x = x0; x < x1; x++) atomicAdd(cnt + y * gx + x, 1u);
+    }
+  }
+}
+
+#ifndef TSPLAT_PRE_MIN_BLOCKS
+#define TSPLAT_PRE_MIN_BLOCKS 4  // 64 registers: 8 CTAs of 4 warps per SM (3 -> 80 registers, 39.6 us; 4 -> 37.3 us at C2)
+#endif
+__global__ void __launch_bounds__(kPreG * kPreMaxWarps, TSPLAT_PRE_MIN_BLOCKS) preprocess_forward_kernel(PreArgs a, Workspace ws, int* out_radii) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
   float* s_op = reinterpret_cast<float*>(smem_raw + 16);
-  float* s_mean = s_op + kPreBlock;
-  float* s_cov = s_mean + 3 * kPreBlock;
-  float* s_sh = s_cov + a.cov_floats * kPreBlock;
-  unsigned int* s_hist = reinterpret_cast<unsigned int*>(s_sh + a.sh_floats * kPreBlock);  // [hist_views][T]
+  float* s_mean = s_op + kPreG;
+  float* s_cov = s_mean + 3 * kPreG;
+  float* s_sh = s_cov + a.cov_floats * kPreG;
 
   const TsplatProblem& p = a.p;
-  const int tid = threadIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nthreads = blockDim.x, nwarps = nthreads >> 5;
   const int b = blockIdx.y;
-  const int g0 = blockIdx.x * kPreBlock;
-  const int cnt = min(kPreBlock, p.G - g0);
+  const int g0 = blockIdx.x * kPreG;
+  const int cnt = min(kPreG, p.G - g0);
   const size_t gbase = (size_t)b * p.G + g0;
   const float* g_mean = p.means + gbase * 3;
   const float* g_cov = p.cov + gbase * a.cov_floats;
   const float* g_sh = p.sh + gbase * a.sh_floats;
   const float* g_op = p.opacity + gbase;
 
-  const bool bulk = a.bulk_ok && cnt == kPreBlock;
-  {  // grid-stride clear of the region bin_emit / sort / ranges expect to be zero
-    const unsigned long long nthr = (unsigned long long)gridDim.x * gridDim.y * kPreBlock;
-    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
-    for (unsigned long long i = ((unsigned long long)blockIdx.y * gridDim.x + blockIdx.x) * kPreBlock + tid;
-         i < a.zero_vec; i += nthr)
-      a.zero_ptr[i] = z;
-  }
+  const bool bulk = a.bulk_ok && cnt == kPreG;
   if (bulk) {
     if (tid == 0) {
       mbar_init(bar, 1);
       mbar_fence_init();
-      const uint32_t bytes = (uint32_t)(kPreBlock * (4 + 12 + 4 * a.cov_floats + 4 * a.sh_floats));
+      const uint32_t bytes = (uint32_t)(kPreG * (4 + 12 + 4 * a.cov_floats + 4 * a.sh_floats));
       mbar_expect_tx(bar, bytes);
-      bulk_g2s(s_op, g_op, kPreBlock * 4, bar);
-      bulk_g2s(s_mean, g_mean, kPreBlock * 12, bar);
-      bulk_g2s(s_cov, g_cov, kPreBlock * 4 * a.cov_floats, bar);
-      bulk_g2s(s_sh, g_sh, kPreBlock * 4 * a.sh_floats, bar);
+      bulk_g2s(s_op, g_op, kPreG * 4, bar);
+      bulk_g2s(s_mean, g_mean, kPreG * 12, bar);
+      bulk_g2s(s_cov, g_cov, kPreG * 4 * a.cov_floats, bar);
+      bulk_g2s(s_sh, g_sh, kPreG * 4 * a.sh_floats, bar);
     }
+  }
+  {  // grid-stride clear of the region bin_emit / sort / ranges expect to be zero (while the slabs are in flight)
+    const unsigned long long nthr = (unsigned long long)gridDim.x * gridDim.y * nthreads;
+    const uint4 z = make_uint4(0u, 0u, 0u, 0u);
+    for (unsigned long long i = ((unsigned long long)blockIdx.y * gridDim.x + blockIdx.x) * nthreads + tid; i < a.zero_vec;
+         i += nthr)
+      a.zero_ptr[i] = z;
+  }
+  if (bulk) {
     __syncthreads();  // barrier init visible before anyone waits
     mbar_wait(bar, 0);
   } else {
-    for (int i = tid; i < cnt; i += kPreBlock) s_op[i] = g_op[i];
-    for (int i = tid; i < cnt * 3; i += kPreBlock) s_mean[i] = g_mean[i];
-    for (int i = tid; i < cnt * a.cov_floats; i += kPreBlock) s_cov[i] = g_cov[i];
-    for (int i = tid; i < cnt * a.sh_floats; i += kPreBlock) s_sh[i] = g_sh[i];
+    for (int i = tid; i < cnt; i += nthreads) s_op[i] = g_op[i];
+    for (int i = tid; i < cnt * 3; i += nthreads) s_mean[i] = g_mean[i];
+    for (int i = tid; i < cnt * a.cov_floats; i += nthreads) s_cov[i] = g_cov[i];
+    for (int i = tid; i < cnt * a.sh_floats; i += nthreads) s_sh[i] = g_sh[i];
     __syncthreads();
   }
-  const bool active = tid < cnt;
-  const int Vg = a.hist_views;
-  if (ws.bucket && Vg > 0) {
-    for (int i = tid; i < Vg * ws.T; i += kPreBlock) s_hist[i] = 0u;
-    __syncthreads();
-  }
-
-  const int g = g0 + tid;
-  const float mu0 = s_mean[3 * tid], mu1 = s_mean[3 * tid + 1], mu2 = s_mean[3 * tid + 2];
+  const bool active = lane < cnt;
+  const int g = g0 + lane;
+  const float mu0 = s_mean[3 * lane], mu1 = s_mean[3 * lane + 1], mu2 = s_mean[3 * lane + 2];
   float craw[6];
   if (p.cov_layout == TSPLAT_COV_TRIU6) {
 #pragma unroll
-    for (int k = 0; k < 6; k++) craw[k] = s_cov[6 * tid + k];
+    for (int k = 0; k < 6; k++) craw[k] = s_cov[6 * lane + k];
   } else {
-    const float* c = s_cov + 9 * tid;
+    const float* c = s_cov + 9 * lane;
     craw[0] = c[0]; craw[1] = c[1]; craw[2] = c[2]; craw[3] = c[4]; craw[4] = c[5]; craw[5] = c[8];
   }
-  const float opac = s_op[tid];
-  const float* my_sh = s_sh + (size_t)tid * a.sh_floats;
+  const float opac = s_op[lane];
+  const float* my_sh = s_sh + (size_t)lane * a.sh_floats;
   const int M = p.sh_coeffs;
   const int gx = ws.tiles_x, gy = ws.tiles_y;
 
-  for (int v = 0; v < p.V; v++) {
+  for (int v = warp; v < p.V; v += nwarps) {  // warp-uniform
     const int n = b * p.V + v;
+    int x0 = 0, y0 = 0, x1 = 0, y1 = 0;
+    bool counted = false;
     if (active) {
     const float* cam = reinterpret_cast<const float*>(p.cams + n);
     const float* vm = cam;        // view[16]
@@ -131,17 +163,11 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a
         const float l1 = mid + sq, l2 = mid - sq;
         const int rad = (int)ceilf(3.0f * sqrtf(fmaxf(l1, l2)));
         const float fpx = ndc2pix(ppx, p.W), fpy = ndc2pix(ppy, p.H);
-        int x0, y0, x1, y1;
         get_rect(fpx, fpy, rad, gx, gy, x0, y0, x1, y1);
         const int area = (x1 - x0) * (y1 - y0);
         if (area != 0) {
           depth = pv.z; radius = rad; px = fpx; py = fpy; touched = (unsigned int)area;
-          if (ws.bucket) {  // bucket path: count the pairs of every (view, tile) while the rectangle is at hand
-            // shared-memory histogram (same-address global reductions serialise at ~75 ns each: measured)
-            unsigned int* cnt_n = Vg > 0 ? s_hist + (v % Vg) * ws.T : ws.tile_count + (size_t)n * ws.T;
-            for (int y = y0; y < y1; y++)
-              for (int x = x0; x < x1; x++) atomicAdd(cnt_n + y * gx + x, 1u);
-          }
+          counted = true;
           con_o = make_float4(q.c * det_inv, -q.b * det_inv, q.a * det_inv, opac);
           if (M > 0) {  // computeColorFromSH (A.5)
             float dx = m.x - __ldg(cam + 32), dy = m.y - __ldg(cam + 33), dz = m.z - __ldg(cam + 34);
@@ -181,7 +207,7 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a
     ws.depths[o] = depth;
     ws.radii[o] = radius;
     {
-      // the record the binning stage copies into sorted order (render.cu reads it as rec0/rec1/rec2)
+      // the per-Gaussian record the render warps gather (render.cu); its last word is the cull threshold of cull.cuh
       float4* gr = ws.grec + o * 3;
       const float tau = radius > 0 ? cull_tau(con_o.x, con_o.y, con_o.z, con_o.w) : 0.0f;
       gr[0] = make_float4(px, py, con_o.x, con_o.y);
@@ -197,17 +223,8 @@ __global__ void __launch_bounds__(kPreBlock) preprocess_forward_kernel(PreArgs a
       ga[0] = z; ga[1] = z; ga[2] = z;
     }
     }  // active
-    if (ws.bucket && Vg > 0 && ((v + 1) % Vg == 0 || v == p.V - 1)) {
-      // flush this group of views: one global reduction per (CTA, non-empty tile)
-      __syncthreads();
-      const int v0 = (v / Vg) * Vg, nv = v - v0 + 1;
-      unsigned int* dst = ws.tile_count + (size_t)(b * p.V + v0) * ws.T;
-      for (int i = tid; i < nv * ws.T; i += kPreBlock) {
-        const unsigned int c = s_hist[i];
-        if (c) { atomicAdd(dst + i, c); s_hist[i] = 0u; }
-      }
-      __syncthreads();
-    }
+    // bucket path: count the pairs of every (view, tile) while the rectangles are at hand
+    if (ws.bucket) count_tiles(ws.tile_count + (size_t)n * ws.T, gx, counted, x0, y0, x1, y1, lane);
   }
 }
 
@@ -231,15 +248,13 @@ cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* 
   // per-scene strides must keep every CTA slab 16-B aligned: G*4, G*12, ... multiples of 16
   const bool stride_ok = p.B == 1 || (p.G % 4 == 0);
   a.bulk_ok = al16(p.means) && al16(p.cov) && al16(p.sh) && al16(p.opacity) && stride_ok &&
-              ((kPreBlock * 4 * a.sh_floats) % 16 == 0);
-  constexpr int kHistMaxBins = 4096;  // 16 KB
-  a.hist_views = ws.T <= kHistMaxBins ? (kHistMaxBins / ws.T < p.V ? kHistMaxBins / ws.T : p.V) : 0;
-  const size_t smem = 16 + sizeof(float) * kPreBlock * (1 + 3 + a.cov_floats + a.sh_floats) +
-                      (ws.bucket ? sizeof(unsigned int) * (size_t)a.hist_views * ws.T : 0);
+              ((kPreG * 4 * a.sh_floats) % 16 == 0);
+  const size_t smem = 16 + sizeof(float) * kPreG * (1 + 3 + a.cov_floats + a.sh_floats);
   cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(preprocess_forward_kernel), (int)smem);
   if (e != cudaSuccess) return e;
-  dim3 grid((p.G + kPreBlock - 1) / kPreBlock, p.B);
-  preprocess_forward_kernel<<<grid, kPreBlock, smem, st>>>(a, ws, out_radii);
+  dim3 grid((p.G + kPreG - 1) / kPreG, p.B);
+  const int warps = p.V < kPreMaxWarps ? p.V : kPreMaxWarps;
+  preprocess_forward_kernel<<<grid, 32 * warps, smem, st>>>(a, ws, out_radii);
   return cudaGetLastError();
 }
 
