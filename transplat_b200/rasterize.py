@@ -358,6 +358,7 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
                     state.problem.flags = (base_flags | _lib.FLAG_BWD_GAUSSIANS_ONLY) & ~_lib.FLAG_REZERO_GRAD_ACC
                     state.problem.g_begin, state.problem.g_count = g0, g1 - g0
                     launch()
+                    # (torch's coalescing manager around these four made the step 30x slower on 2 B200: measured, not used)
                     for t in (g_means, g_cov, g_sh, g_op):
                         works.append(dist.all_reduce(t[0, g0:g1], op=dist.ReduceOp.SUM, group=group, async_op=True))
             finally:  # the problem record is reused by a repeated backward over the same forward state
