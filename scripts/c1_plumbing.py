@@ -11,7 +11,8 @@ this never runs on the GPU box.  The reference files are imported where they lie
 
 Stand-ins for packages that are absent from this image (none of them is on the render path):
   * jaxtyping            annotations only
-  * omegaconf / dacite / pytorch_lightning / wandb / skvideo / matplotlib / xformers / saes: names only (never called)
+  * omegaconf / dacite / pytorch_lightning / wandb / skvideo / matplotlib: names only (never called); xformers and saes
+    stay absent (the reference guards both imports with try / except ImportError)
   * mmcv.utils.ext_loader.load_ext               the compiled deformable-attention op is never called on the CPU path
   * mmcv.ops.multi_scale_deform_attn.multi_scale_deformable_attn_pytorch   its published pure-PyTorch definition
                                                  (bilinear `grid_sample` per level, weighted sum): restated below
@@ -44,6 +45,7 @@ REF = os.environ.get("TSPLAT_REFERENCE_ROOT", "/root/reference")
 import numpy as np
 import torch
 import torch.nn.functional as F
+import torchvision  # noqa: F401  (imported before the stand-ins are installed)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -68,7 +70,13 @@ class _Anything:
 def _stub_module(name: str) -> types.ModuleType:
     m = types.ModuleType(name)
     m.__path__ = []  # a package: submodules resolve through the finder below
-    m.__getattr__ = lambda attr: _Anything  # type: ignore[assignment]
+
+    def _attr(attr):
+        if attr.startswith("__"):
+            raise AttributeError(attr)
+        return _Anything
+
+    m.__getattr__ = _attr  # type: ignore[assignment]
     return m
 
 
@@ -77,21 +85,33 @@ class _StubFinder(importlib.abc.MetaPathFinder, importlib.abc.Loader):
     namespaces so that their __init__ chains (hydra, lightning, dataset registries) are skipped while every MODULE file
     is executed unmodified from where it lies."""
     ABSENT = ("jaxtyping", "omegaconf", "dacite", "pytorch_lightning", "lightning", "wandb", "skvideo", "matplotlib",
-              "xformers", "saes", "mmcv", "e3nn", "lpips", "colorama", "hydra", "beartype", "moviepy", "plyfile", "cv2",
+              "mmcv", "e3nn", "lpips", "colorama", "hydra", "beartype", "moviepy", "plyfile", "cv2",
               "svg", "colorspacious", "tabulate")
+
+    # packages whose __init__ pulls in the training stack (hydra, lightning, dataset / loss registries): path-only
+    SKIP_INIT = {"src", "src.model", "src.model.encoder", "src.model.decoder", "src.dataset", "src.dataset.shims", "src.misc",
+                 "src.geometry", "src.visualization", "src.loss", "src.evaluation", "src.model.encoder.visualization"}
+
+    def __init__(self):
+        # decided once, before this finder is installed: which of the candidates really are absent from the image
+        self.absent = set()
+        for top in self.ABSENT:
+            try:
+                if importlib.util.find_spec(top) is None or top in ("mmcv", "e3nn"):
+                    self.absent.add(top)
+            except (ImportError, ValueError):
+                self.absent.add(top)
 
     def find_spec(self, fullname, path=None, target=None):
         top = fullname.split(".")[0]
-        if top in self.ABSENT:
-            try:
-                if importlib.util.find_spec(top) is not None and top not in ("mmcv", "e3nn"):
-                    return None
-            except (ImportError, ValueError):
-                pass
+        if top in self.absent:
             return importlib.util.spec_from_loader(fullname, self, is_package=True)
         if top == "src":
             d = os.path.join(REF, *fullname.split("."))
             if os.path.isdir(d):
+                init = os.path.join(d, "__init__.py")
+                if fullname not in self.SKIP_INIT and os.path.exists(init):  # a leaf package: its __init__ runs unmodified
+                    return importlib.util.spec_from_file_location(fullname, init, submodule_search_locations=[d])
                 return importlib.util.spec_from_loader(fullname, self, is_package=True)
             f = d + ".py"
             if os.path.exists(f):
@@ -259,6 +279,7 @@ def run(render_views: int = 1) -> dict:
                                rep(gaussians.harmonics), rep(gaussians.opacities))
     depth = ref_cs.render_depth_cuda(tgt["extrinsics"][0], tgt["intrinsics"][0], tgt["near"][0], tgt["far"][0], (256, 256),
                                      rep(gaussians.means), rep(gaussians.covariances), rep(gaussians.opacities), mode="depth")
+    color, depth = color.detach(), depth.detach()
     report["render_s"] = round(time.perf_counter() - t0, 2)
     st = rasterizer_cpu._RasterizeGaussians.last_state
     report["num_rendered_last_pass"] = int(st.num_rendered)

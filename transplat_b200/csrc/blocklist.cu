@@ -51,6 +51,7 @@ __global__ void __launch_bounds__(kBlThreads) block_lists_kernel(Workspace ws, i
   unsigned int c01 = 0, c23 = 0, c45 = 0, c67 = 0;  // pairs of 16-bit counters (a thread sees at most n / 1024 + 1 pairs)
   for (int j = tid; j < n; j += kBlThreads) {
     const unsigned int id = vals[range.x + j];
+    TS_CHECK(id < (unsigned int)G && range.x + (unsigned int)j < ws.d_cap);
     const float4* __restrict__ gr = grec + (size_t)id * kRecFloat4;
     const float4 g0 = gr[0];
     const float cq = gr[1].x, tau = gr[2].w;
@@ -124,6 +125,7 @@ __global__ void __launch_bounds__(kBlThreads) block_lists_kernel(Workspace ws, i
       for (int b = 0; b < 8; b++) {
         if ((m >> b) & 1u) {
           const unsigned int pos = s_start[b] + s_wcnt[warp][b] + rank[b];
+          TS_CHECK(pos < s_lim[b] || s_lim[b] == ws.e_cap);
           if (pos < s_lim[b]) ws.bref[pos] = ref;
         }
       }

@@ -155,6 +155,7 @@ __global__ void __launch_bounds__(256) bucket_emit_kernel(Workspace ws, int G, u
     for (int x = x0; x < x1; x++) {
       const int b = y * ws.tiles_x + x;
       const unsigned int slot = s_base[b] + atomicAdd(&s_cnt[b], 1u);
+      TS_CHECK(slot < ranges[b].y || ranges[b].y == ws.d_cap);
       if (slot < ranges[b].y) pairs[slot] = word;
     }
 }

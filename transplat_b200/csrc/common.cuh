@@ -10,6 +10,16 @@
 #error "libtsplat is written for sm_100a (B200) only"
 #endif
 
+// Checked builds (make EXTRA=-DTSPLAT_CHECKED; scripts/exp_variants.sh): device-side bounds assertions on every index the
+// binning and render kernels derive from data.  compute-sanitizer is closed on the B200 pool this was developed on, so
+// this is the memory check that can be run there (profiles/r02_checked_build.md).
+#ifdef TSPLAT_CHECKED
+#include <assert.h>
+#define TS_CHECK(cond) assert(cond)
+#else
+#define TS_CHECK(cond) ((void)0)
+#endif
+
 namespace tsplat {
 
 constexpr int kTile = TSPLAT_TILE;          // 16x16 pixels per tile (parity contract)

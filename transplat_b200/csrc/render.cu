@@ -191,6 +191,8 @@ __device__ __forceinline__ void prefetch_records(Stream& s, const Workspace& ws,
   if (lane < batch_cnt<kBack>(j, b)) {
     const uint2 ref = lds_u2(ra + 8u * (uint32_t)lane);
     const int view = (int)(j.id >> 3) / ws.T;
+    TS_CHECK(ref.x < (unsigned int)G && ref.y >= 1u && view < ws.N);
+    TS_CHECK((size_t)j.start + batch_lo<kBack>(j, b) + lane < ws.e_cap);
     const char* gr = reinterpret_cast<const char*>(ws.grec + ((size_t)view * G + ref.x) * kRecFloat4);
     const uint32_t dst = s.rec_addr + (uint32_t)(s.tile_sel * kRecTileBytes + lane * kRecBytes);
     cp_async16(dst, gr);
@@ -331,6 +333,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_
       if (b > 0 && (b * kWBatch) % kSegLen == 0) {
         // per-pixel state in front of reference b * 32 of this list: render_backward restarts from it, so that the
         // list's segments are independent work units (blocklist.cu: segment_jobs_kernel)
+        TS_CHECK((size_t)(cur.start / kSegLen) + (size_t)(b * kWBatch / kSegLen) < ws.e_cap / kSegLen + 2);
         float* ck = ws.ckpt + ((size_t)(cur.start / kSegLen) + (size_t)(b * kWBatch / kSegLen)) * kCkptFloats + lane;
         ck[0] = T; ck[32] = C[0]; ck[64] = C[1]; ck[96] = C[2]; ck[128] = CH == 4 ? C[CH - 1] : 0.0f;
       }
@@ -378,6 +381,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_
         if (rem) at_part = atomicAdd(&ws.ctl->seg_part, 1u);
       }
       at_full = __shfl_sync(0xffffffffu, at_full, 0);
+      TS_CHECK(at_full + nfull + at_part < ws.seg_cap);
       for (unsigned int k = lane; k < nfull; k += 32) ws.segs[at_full + k] = make_uint4(cur.start, len, cur.id, k);
       if (lane == 0 && rem) ws.segs[ws.seg_cap - 1 - at_part] = make_uint4(cur.start, len, cur.id, nfull);
     }
@@ -545,6 +549,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
       // checkpoint render_forward left in front of reference hi
       const unsigned int hi = cur_k * kSegLen + (unsigned int)count;
       const bool restart = hi < cur_ll;
+      TS_CHECK(!restart || (size_t)(cur_ls / kSegLen) + hi / kSegLen < ws.e_cap / kSegLen + 2);
       const float* ck = ws.ckpt + ((size_t)(cur_ls / kSegLen) + hi / kSegLen) * kCkptFloats + lane;
       // The reference keeps accum_rec[ch] (colour behind the current entry) per channel and forms
       // dL/dalpha = sum_ch (c[ch] - accum_rec[ch]) dL_dpix[ch]; dL_dpix is constant along the list, so the recurrence
@@ -657,6 +662,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
           Mx += __shfl_xor_sync(full, Mx, 1);
           G2 += __shfl_xor_sync(full, G2, 1);
           const float r = (lane_bits & 32) ? G2 : Mx;
+          TS_CHECK(__float_as_uint(a2.z) < (unsigned int)G);
           if (my_red) red_global_add(acc_lane + (size_t)__float_as_uint(a2.z) * kAccFloats, r);
         }
       }
