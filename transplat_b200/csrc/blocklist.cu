@@ -20,10 +20,16 @@
 
 namespace tsplat {
 
-constexpr int kBlThreads = 512;
+#ifndef TSPLAT_BL_THREADS
+#define TSPLAT_BL_THREADS 512
+#endif
+#ifndef TSPLAT_BL_MIN_BLOCKS
+#define TSPLAT_BL_MIN_BLOCKS 4  // 32 registers, 4 CTAs per SM: 2 / 3 / 4 -> 53.7 / 53.9 / 49.5 us at C2
+#endif
+constexpr int kBlThreads = TSPLAT_BL_THREADS;
 constexpr int kBlWarps = kBlThreads / 32;
 
-__global__ void __launch_bounds__(kBlThreads) block_lists_kernel(Workspace ws, int G, const unsigned int* __restrict__ vals) {
+__global__ void __launch_bounds__(kBlThreads, TSPLAT_BL_MIN_BLOCKS) block_lists_kernel(Workspace ws, int G, const unsigned int* __restrict__ vals) {
   __shared__ unsigned int s_cnt[kBlocksPerTile];               // pass 1: entries per block
   __shared__ unsigned int s_start[kBlocksPerTile];             // first entry of each block's list (clipped to e_cap)
   __shared__ unsigned int s_lim[kBlocksPerTile];               // one past its last usable entry

@@ -43,6 +43,27 @@ __device__ __forceinline__ float cull_tau(float A, float B, float C, float o) {
 __device__ __forceinline__ unsigned int cull_block_mask(float4 a0 /* x, y, A, B */, float Cq, float tau, float tileX0,
                                                         float tileY0) {
   unsigned int mask = 0;
+  // Conservative bounding box of {q <= tau} first: half-widths sqrt(2 tau C / det), sqrt(2 tau A / det), widened by
+  // 0.1 % + 0.02 px; only the block columns / rows it overlaps get the exact test below (2-4 of the 8 blocks for an
+  // encoder-sized Gaussian).  Degenerate conics (tau = +inf, det <= 0, NaN) keep the full range.
+  unsigned int cols = 3u, rows = 15u;
+  if (!(tau > -3.0e38f)) return 0u;  // opacity below 1/255: alpha < 1/255 on every pixel
+  {
+    const float det = a0.z * Cq - a0.w * a0.w;
+    if (det > 0.0f && tau < 3.0e38f) {
+      float rdet;
+      asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rdet) : "f"(det));
+      const float s = 2.0f * fmaxf(tau, 0.0f) * rdet;
+      const float ex = sqrtf(s * Cq) * 1.001f + 0.02f, ey = sqrtf(s * a0.z) * 1.001f + 0.02f;
+      if (ex == ex && ey == ey) {
+        const float lx = a0.x - ex - tileX0, hx = a0.x + ex - tileX0;  // the box in tile coordinates
+        const float ly = a0.y - ey - tileY0, hy = a0.y + ey - tileY0;
+        cols = (lx <= 7.0f && hx >= 0.0f ? 1u : 0u) | (lx <= 15.0f && hx >= 8.0f ? 2u : 0u);
+        rows = (ly <= 3.0f && hy >= 0.0f ? 1u : 0u) | (ly <= 7.0f && hy >= 4.0f ? 2u : 0u) |
+               (ly <= 11.0f && hy >= 8.0f ? 4u : 0u) | (ly <= 15.0f && hy >= 12.0f ? 8u : 0u);
+      }
+    }
+  }
   // raw reciprocals: A, C of a kept Gaussian are normal positive numbers; anything else gives inf/NaN, which the
   // clamps turn back into a point of the box, and tau = +inf keeps a degenerate conic anyway
   float rA, rC;
@@ -50,12 +71,14 @@ __device__ __forceinline__ unsigned int cull_block_mask(float4 a0 /* x, y, A, B 
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rC) : "f"(Cq));
 #pragma unroll
   for (int cx = 0; cx < 2; cx++) {
+    if (!((cols >> cx) & 1u)) continue;
     const float a_lo = tileX0 + 8.0f * cx - a0.x, a_hi = a_lo + 7.0f;
     const float ax = fminf(fmaxf(0.0f, a_lo), a_hi);
     const float dy1_free = -a0.w * ax * rC;
     const float q1x = a0.z * ax * ax;
 #pragma unroll
     for (int ry = 0; ry < 4; ry++) {
+      if (!((rows >> ry) & 1u)) continue;
       const float b_lo = tileY0 + 4.0f * ry - a0.y, b_hi = b_lo + 3.0f;
       const float by = fminf(fmaxf(0.0f, b_lo), b_hi);
       const float dy1 = fminf(fmaxf(dy1_free, b_lo), b_hi);
