@@ -498,11 +498,12 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
         cam = [t[None].to(dev) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
         one = torch.ones((), device=dev)
 
-        def step(reduce=True, overlap=0):
+        def step(reduce=True, overlap=0, fused=False):
             leaves = [stat[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
             g = Gaussians(*leaves)
             if reduce:
-                out, _ = forward_view_sharded(decoder, g, *cam, (hw, hw), depth_mode="depth", overlap_chunks=overlap)
+                out, _ = forward_view_sharded(decoder, g, *cam, (hw, hw), depth_mode="depth", overlap_chunks=overlap,
+                                              fused_reduce=fused)
             else:  # the same local views, no collective: what the step costs without the exchange
                 idx = torch.tensor(mine, device=dev)
                 out = decoder.forward(g, *(c[:, idx] for c in cam), (hw, hw), depth_mode="depth")
@@ -526,27 +527,39 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
 
         t_plain = time_it(lambda: step(True, 0), steps)
         t_overlap = time_it(lambda: step(True, chunks), steps) if chunks > 1 else None
+        try:  # the reduction inside the producing kernel (multimem.red through NVLS multicast memory)
+            t_fused = time_it(lambda: step(True, 0, True), steps)
+        except Exception as exc:
+            print(f"[bench] fused multimem reduction unavailable ({exc!r})", file=sys.stderr, flush=True)
+            t_fused = None
         t_local = time_it(lambda: step(False), steps)
         # the collective alone, on a slab of the same size
         from transplat_b200.rasterize import _pad64
         n_slab = _pad64(G * 3) + _pad64(G * 9) + _pad64(G * 75) + G
         slab = torch.zeros(n_slab, dtype=torch.float32, device=dev)
         t_ar = time_it(lambda: dist.all_reduce(slab), max(steps, 10))
-        best = min(t for t in (t_plain, t_overlap) if t is not None)
+        best = min(t for t in (t_plain, t_overlap, t_fused) if t is not None)
         nbytes = n_slab * 4
         return {"shape": name, "views": V, "views_per_rank": per_rank, "gaussians": G, "image": [hw, hw], "steps": steps,
                 "ms_per_step": round(best, 4), "views_per_s": round(V / (best * 1e-3), 1),
                 "ms_per_step_one_all_reduce": round(t_plain, 4),
                 "ms_per_step_chunked_overlap": round(t_overlap, 4) if t_overlap is not None else None, "chunks": chunks,
+                "ms_per_step_fused_multimem": round(t_fused, 4) if t_fused is not None else None,
+                "fastest": "fused_multimem" if best == t_fused else ("one_all_reduce" if best == t_plain else "chunked_overlap"),
                 "ms_per_step_without_collective": round(t_local, 4),
-                "all_reduce_exposed_ms": round(best - t_local, 4),
+                "exchange_exposed_ms": round(best - t_local, 4),
+                "all_reduce_exposed_ms": round(t_plain - t_local, 4),
                 "all_reduce_alone_ms": round(t_ar, 4), "all_reduce_bytes": int(nbytes),
                 "all_reduce_bus_gbs": round(2.0 * (world - 1) / world * nbytes / (t_ar * 1e-3) / 1e9, 1),
                 "launch": "eager (one process per GPU, NCCL on its own stream)"}
 
     out = {"what": "one scene, target views split round-robin over the ranks, Gaussians replicated, per-Gaussian gradients "
-                   "summed over the ranks (ncclAllReduce, float32 sum): the only collective on the path (SURVEY 8e); "
-                   "fwd+bwd through transplat_b200.parallel.forward_view_sharded, device time, max over ranks",
+                   "summed over the ranks: the only exchange on the path (SURVEY 8e).  one_all_reduce = ncclAllReduce of "
+                   "the flat gradient slab behind the backward kernels; chunked_overlap = per-Gaussian-range all-reduces "
+                   "under the next range's kernels; fused_multimem = preprocess_backward adds its values with "
+                   "multimem.red.add.f32 through the multicast alias of a symmetric slab (NVLS: the switch reduces into "
+                   "every rank's replica while the kernel computes; no collective follows).  fwd+bwd through "
+                   "transplat_b200.parallel.forward_view_sharded, device time, max over ranks",
            "c2_shape": one_shape("C2 shape: 131072 Gaussians, 256x256, 4 views per rank", HW, VIEWS, min(args.steps, 30), 2)}
     if args.c5:
         out["c5_shape"] = one_shape("C5 stress: 2097152 Gaussians, 1024x1024, 8 views per rank", 1024, 8, 5, 3)

@@ -75,6 +75,15 @@ extern "C" {
                                               gradients of one range over the ranks while the next is computed
                                               (transplat_b200/parallel.py) */
 
+#define TSPLAT_FLAG_BWD_MULTIMEM 32         /* tsplat_backward[_mse]: the four per-Gaussian gradient pointers are MULTICAST
+                                              addresses of symmetric slabs replicated on every GPU of an NVSwitch domain
+                                              (cuMulticast* / torch symmetric memory).  The per-Gaussian kernel then ADDS
+                                              its values with multimem.red.add.f32: the switch reduces them into every
+                                              replica, so after a barrier every rank holds the gradients summed over all
+                                              ranks' views - the all-reduce of view sharding happens inside the
+                                              kernel that produces the gradients, overlapped with it.  The caller zeroes
+                                              its replica and synchronises the ranks before and after the call. */
+
 /* fused depth channel (render_depth_cuda, cuda_splatting.py:375-417) */
 #define TSPLAT_DEPTH_NONE 0
 #define TSPLAT_DEPTH_DEPTH 1

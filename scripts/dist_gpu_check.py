@@ -32,7 +32,8 @@ g_full = torch.autograd.grad(loss, L0)
 # view-sharded: this rank renders views rank, rank+world, ...
 L1 = leaves()
 out_s, mine = forward_view_sharded(dec, Gaussians(*L1), *cam, (HW, HW), depth_mode="depth",
-                                   overlap_chunks=int(os.environ.get("OVERLAP", "0")))
+                                   overlap_chunks=int(os.environ.get("OVERLAP", "0")),
+                                   fused_reduce=os.environ.get("FUSED_REDUCE", "0") == "1")
 idx = torch.tensor(mine, device=dev)
 loss_s = ((out_s.color[0] - target[idx]) ** 2).sum() + (out_s.depth[0] * dLd[idx]).sum()
 g_shard = torch.autograd.grad(loss_s, L1)

@@ -19,6 +19,7 @@ FLAG_SORT_ONESWEEP = 2
 FLAG_DEBUG = 4
 FLAG_BWD_RENDER_ONLY = 8
 FLAG_BWD_GAUSSIANS_ONLY = 16
+FLAG_BWD_MULTIMEM = 32
 DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "log": 4}
 
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",

@@ -368,8 +368,10 @@ static int backward_impl(const TsplatProblem* p, void* workspace, uint64_t works
   }
   {
     StageTimer t(kStPreB, st);
+    const bool multimem = (p->flags & TSPLAT_FLAG_BWD_MULTIMEM) != 0;
+    if (multimem && dL_dmeans2D) { set_error("backward: TSPLAT_FLAG_BWD_MULTIMEM does not cover dL_dmeans2D"); return TSPLAT_EINVAL; }
     e = debug_sync(p, st, launch_preprocess_backward(*p, ws, dL_dmeans, dL_dcov, dL_dsh, dL_dopacity, dL_dmeans2D,
-                                                     g_begin, g_count, st));
+                                                     g_begin, g_count, multimem, st));
   }
   if (e != cudaSuccess) return cuda_fail("preprocess_backward", e);
   return TSPLAT_OK;

@@ -147,7 +147,7 @@ cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, 
                                    const float* dL_ddepth, const TsplatMse* mse, cudaStream_t st);
 cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& ws, float* dL_dmeans,
                                        float* dL_dcov, float* dL_dsh, float* dL_dopacity,
-                                       float* dL_dmeans2D, int g_begin, int g_count, cudaStream_t st);
+                                       float* dL_dmeans2D, int g_begin, int g_count, bool multimem, cudaStream_t st);
 cudaError_t launch_pack_cameras(int N, const float* extrinsics, const float* intrinsics, const float* near_,
                                 const float* far_, const float* bg, int bg_stride, int scale_invariant,
                                 TsplatCamera* out, cudaStream_t st);

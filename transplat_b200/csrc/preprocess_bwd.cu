@@ -25,6 +25,7 @@ constexpr int kPart = 11;         // partial sums per (view, Gaussian): mean 3, 
 struct PreBwdArgs {
   TsplatProblem p;
   int cov_floats, sh_floats, bulk_ok, out_bulk_ok;
+  int multimem;        // outputs are multicast addresses: add with multimem.red instead of storing (view sharding)
   int g_begin, g_end;  // Gaussian range of this launch (every scene); g_begin is a multiple of kPreBwdBlock
   float* dL_dmeans;
   float* dL_dcov;
@@ -32,6 +33,17 @@ struct PreBwdArgs {
   float* dL_dopacity;
   float* dL_dmeans2D;
 };
+
+// multimem.red: one instruction adds the value(s) into EVERY GPU's replica of a multicast-mapped buffer; the NVSwitch
+// performs the reduction (NVLS).  sm_90+ / PTX 8.1.
+__device__ __forceinline__ void mc_red_add(float* mc_addr, float v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.f32 [%0], %1;" ::"l"(mc_addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void mc_red_add_v4(float* mc_addr, float4 v) {
+  asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
 
 // SH basis values (stored through `store(k, value)`) and dL/d(direction) += sum_k dbasis_k/d(direction) * w(k), where
 // w(k) = sum_ch sh[k][ch] * dL/dcolour[ch] is produced on demand - same polynomials as geom.cuh: sh_basis.
@@ -344,7 +356,24 @@ __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) pre
     for (int i = 0; i < kMaxOut; i++)
       if (out_r0 + i < a.sh_floats) so[i] = dsh[i];
   }
-  if (bulk && a.out_bulk_ok) {
+  if (a.multimem) {
+    // view sharding: this rank's sums go straight into every rank's gradient slab, reduced by the switch; Gaussians no
+    // local view sees send nothing
+    __syncthreads();
+    const int nfl = cnt * a.sh_floats;
+    if ((reinterpret_cast<uintptr_t>(g_dsh) & 15u) == 0) {
+      const float4* s4 = reinterpret_cast<const float4*>(s_sh);
+      for (int i = tid; i < nfl / 4; i += nthreads) {
+        const float4 v = s4[i];
+        if (v.x != 0.0f || v.y != 0.0f || v.z != 0.0f || v.w != 0.0f) mc_red_add_v4(g_dsh + 4 * i, v);
+      }
+      for (int i = (nfl & ~3) + tid; i < nfl; i += nthreads)
+        if (s_sh[i] != 0.0f) mc_red_add(g_dsh + i, s_sh[i]);
+    } else {
+      for (int i = tid; i < nfl; i += nthreads)
+        if (s_sh[i] != 0.0f) mc_red_add(g_dsh + i, s_sh[i]);
+    }
+  } else if (bulk && a.out_bulk_ok) {
     fence_proxy_async();
     __syncthreads();
     if (tid == 0) {
@@ -375,6 +404,18 @@ __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) pre
       for (int k = 0; k < 10; k++) sum[k] += mp[k];
     }
     const size_t og = (size_t)b * p.G + g;
+    if (a.multimem) {
+      auto add = [](float* q, float v) { if (v != 0.0f) mc_red_add(q, v); };
+      add(a.dL_dmeans + og * 3 + 0, sum[0]); add(a.dL_dmeans + og * 3 + 1, sum[1]); add(a.dL_dmeans + og * 3 + 2, sum[2]);
+      add(a.dL_dopacity + og, sum[9]);
+      if (p.cov_layout == TSPLAT_COV_TRIU6) {
+#pragma unroll
+        for (int k = 0; k < 6; k++) add(a.dL_dcov + og * 6 + k, sum[3 + k]);
+      } else {
+        float* c = a.dL_dcov + og * 9;
+        add(c + 0, sum[3]); add(c + 1, sum[4]); add(c + 2, sum[5]); add(c + 4, sum[6]); add(c + 5, sum[7]); add(c + 8, sum[8]);
+      }
+    } else {
     a.dL_dmeans[og * 3 + 0] = sum[0]; a.dL_dmeans[og * 3 + 1] = sum[1]; a.dL_dmeans[og * 3 + 2] = sum[2];
     a.dL_dopacity[og] = sum[9];
     if (p.cov_layout == TSPLAT_COV_TRIU6) {
@@ -385,12 +426,14 @@ __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) pre
       c[0] = sum[3]; c[1] = sum[4]; c[2] = sum[5]; c[3] = 0.f; c[4] = sum[6]; c[5] = sum[7];
       c[6] = 0.f; c[7] = 0.f; c[8] = sum[8];
     }
+    }
   }
+  if (a.multimem) __threadfence_system();
 }
 
 cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& ws, float* dL_dmeans, float* dL_dcov,
                                        float* dL_dsh, float* dL_dopacity, float* dL_dmeans2D, int g_begin, int g_count,
-                                       cudaStream_t st) {
+                                       bool multimem, cudaStream_t st) {
   if (g_count <= 0) return cudaSuccess;
   PreBwdArgs a;
   a.p = p;
@@ -401,6 +444,7 @@ cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& 
   const bool stride_ok = p.B == 1 || (p.G % 4 == 0);
   a.bulk_ok = al16(p.means) && al16(p.cov) && al16(p.sh) && stride_ok && ((kBwdG * 4 * a.sh_floats) % 16 == 0);
   a.out_bulk_ok = al16(dL_dsh) && stride_ok;
+  a.multimem = multimem ? 1 : 0;
   a.dL_dmeans = dL_dmeans; a.dL_dcov = dL_dcov; a.dL_dsh = dL_dsh; a.dL_dopacity = dL_dopacity;
   a.dL_dmeans2D = dL_dmeans2D;
   const int warps = p.V <= 4 ? 4 : kBwdMaxWarps;

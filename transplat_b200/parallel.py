@@ -4,8 +4,13 @@
   (the pattern of the reference's Lightning DDP over scenes, src/main.py:117-129).
 * view sharding — one scene's target views split over ranks (view j -> rank j mod N), Gaussians
   replicated; forward needs no communication; backward sums the per-Gaussian gradients
-  (means 3 + covariance 9 + SH 75 + opacity 1 floats per Gaussian) with ONE all-reduce over a
-  single flat slab.  This is the only collective on the path.
+  (means 3 + covariance 9 + SH 75 + opacity 1 floats per Gaussian) over the ranks - the only
+  exchange on the path.  Two ways:
+    - ONE NCCL all-reduce over a single flat slab behind the backward kernels (default), or
+    - fused (``fused_reduce=True``): the kernel that PRODUCES the gradients (preprocess_backward) adds them with
+      ``multimem.red.add.f32`` through the multicast alias of a symmetric slab (torch symmetric memory, NVLS): the
+      NVSwitch reduces every value into every rank's replica while the kernel is still computing, so the reduction
+      overlaps the math and no collective follows - only a barrier.
 """
 from __future__ import annotations
 
@@ -15,6 +20,48 @@ import torch
 import torch.distributed as dist
 
 from .decoder import DecoderOutput, Gaussians
+
+
+class SymmetricGradSlab:
+    """Gradient slab replicated on every rank of an NVSwitch domain with a multicast alias (torch symmetric memory).
+    Two replicas are cycled, so the gradients returned by one backward stay valid until the backward after the next.
+
+    begin_step(): zero this rank's replica, then a device-side barrier (every replica is zero before any rank adds);
+    end_step():   a device-side barrier (every rank's producing kernel has finished: the sums are complete everywhere).
+    Both only enqueue work on the current stream."""
+    _cache = {}
+
+    def __init__(self, group, device, numel):
+        import torch.distributed._symmetric_memory as symm
+        self.bufs, self.hdls = [], []
+        for _ in range(2):
+            t = symm.empty(numel, dtype=torch.float32, device=device)
+            h = symm.rendezvous(t, group if group is not None else dist.group.WORLD)
+            if not h.multicast_ptr:
+                raise RuntimeError("symmetric memory on this system has no multicast (NVLS) support: use the NCCL path")
+            self.bufs.append(t)
+            self.hdls.append(h)
+        self.i = 0
+
+    @classmethod
+    def get(cls, group, device, numel):
+        key = (id(group), device.index, int(numel))
+        if key not in cls._cache:
+            cls._cache[key] = cls(group, device, int(numel))
+        return cls._cache[key]
+
+    @property
+    def multicast_ptr(self) -> int:
+        return int(self.hdls[self.i].multicast_ptr)
+
+    def begin_step(self):
+        self.i ^= 1
+        self.bufs[self.i].zero_()
+        self.hdls[self.i].barrier(channel=0)
+        return self.bufs[self.i]
+
+    def end_step(self):
+        self.hdls[self.i].barrier(channel=1)
 
 
 def shard_indices(n: int, rank: int, world: int) -> list:
@@ -67,24 +114,27 @@ def replicate_with_summed_grads(gaussians: Gaussians, group=None) -> Gaussians:
 
 
 def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
-                         depth_mode: Optional[str] = None, group=None, overlap_chunks: int = 0) -> tuple:
+                         depth_mode: Optional[str] = None, group=None, overlap_chunks: int = 0,
+                         fused_reduce: bool = False) -> tuple:
     """Each rank renders views rank, rank+N, ... of every scene in the batch.  Returns
     (DecoderOutput for the local views, list of the global view indices rendered here).  Backward
     through the output all-reduces the per-Gaussian gradients once - or, with ``overlap_chunks`` > 1 (one scene per
     call, CUDA decoder), range by range inside the rasterizer's backward, each all-reduce running under the kernels of
-    the next Gaussian range (713 MB at C5)."""
+    the next Gaussian range (713 MB at C5); with ``fused_reduce`` the
+    per-Gaussian kernel itself reduces them through NVLS multicast memory (SymmetricGradSlab)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     v = extrinsics.shape[1]
     mine = shard_indices(v, rank, world)
     staged = world > 1 and overlap_chunks > 1 and gaussians.means.shape[0] == 1 and gaussians.means.is_cuda
-    if world > 1 and not staged:
+    fused = world > 1 and fused_reduce and gaussians.means.is_cuda
+    if world > 1 and not staged and not fused:
         gaussians = replicate_with_summed_grads(gaussians, group)
     if not mine:
         # a rank without views would skip backward and leave the others waiting in the all-reduce
         raise ValueError(f"view sharding needs at least one view per rank (views={v}, ranks={world})")
     idx = torch.tensor(mine, device=extrinsics.device)
-    extra = {"grad_reduce": (group, int(overlap_chunks))} if staged else {}
+    extra = {"grad_reduce": (group, "multimem")} if fused else ({"grad_reduce": (group, int(overlap_chunks))} if staged else {})
     out = decoder.forward(gaussians, extrinsics[:, idx], intrinsics[:, idx], near[:, idx], far[:, idx], image_shape,
                           depth_mode=depth_mode, **extra)
     return out, mine

@@ -113,8 +113,10 @@ class RenderConfig:
     d_cap: int | None = None
     debug: bool = False        # reference debug=True: synchronise and check after every stage
     sort: str | None = None    # None -> TSPLAT_SORT env ("bucket" default) | "bucket" | "onesweep"
-    # view sharding (parallel.py): (process group, chunks).  The backward then sums the per-Gaussian gradients over
-    # the group itself, one Gaussian range at a time, each all-reduce overlapping the next range's kernels
+    # view sharding (parallel.py): (process group, chunks) - the backward sums the per-Gaussian gradients over the group
+    # itself, one Gaussian range at a time, each all-reduce overlapping the next range's kernels - or
+    # (process group, "multimem") - the per-Gaussian kernel adds its values with multimem.red into a symmetric slab
+    # replicated on every GPU of the NVSwitch domain (parallel.SymmetricGradSlab): no separate collective
     grad_reduce: tuple | None = None
 
 
@@ -304,7 +306,14 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
         offs = [0]
         for n_ in sizes[:-1]:
             offs.append(offs[-1] + _pad64(n_))
-        slab = torch.empty(offs[-1] + sizes[-1], dtype=torch.float32, device=dev)
+        reduce = cfg.grad_reduce
+        multimem = reduce is not None and reduce[1] == "multimem"
+        if multimem:
+            from .parallel import SymmetricGradSlab
+            sym = SymmetricGradSlab.get(reduce[0], dev, offs[-1] + sizes[-1])
+            slab = sym.begin_step()  # this rank's replica, zeroed; every rank has zeroed its own before anyone adds
+        else:
+            slab = torch.empty(offs[-1] + sizes[-1], dtype=torch.float32, device=dev)
         g_means, g_cov, g_sh, g_op = (slab[o:o + n_].view(t.shape)
                                       for o, n_, t in zip(offs, sizes, (means, cov, sh, opacity)))
         g_m2d = (torch.empty((N, means.shape[1], 3), dtype=torch.float32, device=dev)
@@ -320,20 +329,32 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
             m = TsplatMse(target=target.data_ptr(), loss_sum=0, color=color.data_ptr(), dL_dloss=grad_loss.data_ptr(),
                           scale=scale, loss_scale=0.0, psnr=0)
 
+        # where the kernels write the gradients: the slab itself, or - multimem - the slab's multicast alias
+        outs = [_ptr(t) for t in (g_means, g_cov, g_sh, g_op)]
+        if multimem:
+            outs = [C.c_void_p(sym.multicast_ptr + 4 * o) for o in offs]
+
         def launch():
             if fused:
                 _lib.check(L.tsplat_backward_mse(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
-                                                 state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means),
-                                                 _ptr(g_cov), _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.byref(m),
-                                                 C.c_void_p(stream.cuda_stream)), "tsplat_backward_mse")
+                                                 state.d_cap, _ptr(grad_color), _ptr(grad_depth), *outs, _ptr(g_m2d),
+                                                 C.byref(m), C.c_void_p(stream.cuda_stream)), "tsplat_backward_mse")
             else:
                 _lib.check(L.tsplat_backward(C.byref(state.problem), _ptr(state.workspace), state.layout.total_bytes,
-                                             state.d_cap, _ptr(grad_color), _ptr(grad_depth), _ptr(g_means), _ptr(g_cov),
-                                             _ptr(g_sh), _ptr(g_op), _ptr(g_m2d), C.c_void_p(stream.cuda_stream)),
-                           "tsplat_backward")
+                                             state.d_cap, _ptr(grad_color), _ptr(grad_depth), *outs, _ptr(g_m2d),
+                                             C.c_void_p(stream.cuda_stream)), "tsplat_backward")
 
-        reduce = cfg.grad_reduce
-        if reduce is None or means.shape[0] != 1:
+        if multimem:
+            if g_m2d is not None:
+                raise RuntimeError("grad_reduce='multimem' does not cover the screen-space gradient (level 1 only)")
+            base_flags = state.problem.flags
+            try:
+                state.problem.flags = base_flags | _lib.FLAG_BWD_MULTIMEM
+                launch()
+            finally:
+                state.problem.flags = base_flags
+            sym.end_step()  # every rank's kernel has finished: the replicas hold the sums over all ranks' views
+        elif reduce is None or means.shape[0] != 1:
             launch()
             if reduce is not None:  # several scenes per call: their Gaussian ranges are not contiguous in the slab
                 import torch.distributed as dist
