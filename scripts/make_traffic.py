@@ -8,7 +8,7 @@ hdr, units, data = rows[0], rows[1], rows[2:]
 ix = {h: i for i, h in enumerate(hdr)}
 scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 stage_of = {"preprocess_forward_kernel": "preprocess", "bucket_scan_kernel": "bin_emit", "bucket_emit_kernel": "bin_emit",
-            "tile_sort_gather_kernel": "sort", "big_tile_sort_gather_kernel": "sort", "gather_records_kernel": "sort",
+            "tile_sort_gather_kernel": "sort", "big_tile_sort_gather_kernel": "sort", "block_lists_kernel": "ranges_gather",
             "render_forward_kernel": "render_forward", "render_backward_kernel": "render_backward",
             "preprocess_backward_kernel": "preprocess_backward"}
 per_kernel = {}
