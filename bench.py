@@ -498,12 +498,12 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
         cam = [t[None].to(dev) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
         one = torch.ones((), device=dev)
 
-        def step(reduce=True, overlap=0, fused=False):
+        def step(reduce=True, overlap=0, fused=False, nvls=False, ctas=0):
             leaves = [stat[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
             g = Gaussians(*leaves)
             if reduce:
                 out, _ = forward_view_sharded(decoder, g, *cam, (hw, hw), depth_mode="depth", overlap_chunks=overlap,
-                                              fused_reduce=fused)
+                                              fused_reduce=fused, nvls_reduce=nvls, nvls_ctas=ctas)
             else:  # the same local views, no collective: what the step costs without the exchange
                 idx = torch.tensor(mine, device=dev)
                 out = decoder.forward(g, *(c[:, idx] for c in cam), (hw, hw), depth_mode="depth")
@@ -532,20 +532,44 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
         except Exception as exc:
             print(f"[bench] fused multimem reduction unavailable ({exc!r})", file=sys.stderr, flush=True)
             t_fused = None
+        from transplat_b200.rasterize import _pad64
+        n_slab = _pad64(G * 3) + _pad64(G * 9) + _pad64(G * 75) + _pad64(G)
+        # our own exchange kernel through the switch (csrc/exchange.cu): whole slab behind the kernels, and range by
+        # range on a side stream under the per-Gaussian kernel of the next range; then alone, over its grid size
+        t_nvls = t_nvls_chunked = None
+        nvls_alone = {}
+        try:
+            from transplat_b200.parallel import SymmetricGradSlab
+            t_nvls = time_it(lambda: step(True, 0, nvls=True), steps)
+            t_nvls_chunked = time_it(lambda: step(True, chunks, nvls=True), steps) if chunks > 1 else None
+            sym = SymmetricGradSlab.get(None, dev, n_slab)
+
+            def alone(c):
+                sym.barrier(0)
+                sym.all_reduce([(0, n_slab)], c)
+                sym.barrier(0)
+            for c in (16, 32, 64, 148, 296):
+                nvls_alone[str(c)] = round(time_it(lambda: alone(c), max(steps, 10)), 4)
+        except Exception as exc:
+            print(f"[bench] NVLS exchange unavailable ({exc!r})", file=sys.stderr, flush=True)
         t_local = time_it(lambda: step(False), steps)
         # the collective alone, on a slab of the same size
-        from transplat_b200.rasterize import _pad64
-        n_slab = _pad64(G * 3) + _pad64(G * 9) + _pad64(G * 75) + G
         slab = torch.zeros(n_slab, dtype=torch.float32, device=dev)
         t_ar = time_it(lambda: dist.all_reduce(slab), max(steps, 10))
-        best = min(t for t in (t_plain, t_overlap, t_fused) if t is not None)
+        named = {"one_all_reduce": t_plain, "chunked_overlap": t_overlap, "fused_multimem": t_fused, "nvls_two_shot": t_nvls,
+                 "nvls_two_shot_chunked": t_nvls_chunked}
+        fastest = min((k for k in named if named[k] is not None), key=lambda k: named[k])
+        best = named[fastest]
         nbytes = n_slab * 4
         return {"shape": name, "views": V, "views_per_rank": per_rank, "gaussians": G, "image": [hw, hw], "steps": steps,
                 "ms_per_step": round(best, 4), "views_per_s": round(V / (best * 1e-3), 1),
                 "ms_per_step_one_all_reduce": round(t_plain, 4),
                 "ms_per_step_chunked_overlap": round(t_overlap, 4) if t_overlap is not None else None, "chunks": chunks,
                 "ms_per_step_fused_multimem": round(t_fused, 4) if t_fused is not None else None,
-                "fastest": "fused_multimem" if best == t_fused else ("one_all_reduce" if best == t_plain else "chunked_overlap"),
+                "ms_per_step_nvls_two_shot": round(t_nvls, 4) if t_nvls is not None else None,
+                "ms_per_step_nvls_two_shot_chunked": round(t_nvls_chunked, 4) if t_nvls_chunked is not None else None,
+                "nvls_exchange_alone_ms_by_ctas": nvls_alone,
+                "fastest": fastest,
                 "ms_per_step_without_collective": round(t_local, 4),
                 "exchange_exposed_ms": round(best - t_local, 4),
                 "all_reduce_exposed_ms": round(t_plain - t_local, 4),
@@ -558,7 +582,10 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
                    "the flat gradient slab behind the backward kernels; chunked_overlap = per-Gaussian-range all-reduces "
                    "under the next range's kernels; fused_multimem = preprocess_backward adds its values with "
                    "multimem.red.add.f32 through the multicast alias of a symmetric slab (NVLS: the switch reduces into "
-                   "every rank's replica while the kernel computes; no collective follows).  fwd+bwd through "
+                   "every rank's replica while the kernel computes; no collective follows); nvls_two_shot = the kernels write "
+                   "this rank's replica of a symmetric slab, our own kernel (csrc/exchange.cu: multimem.ld_reduce + "
+                   "multimem.st) sums the replicas in place through the switch - whole slab, or (chunked) range by range on "
+                   "a side stream under the per-Gaussian kernel of the next range.  fwd+bwd through "
                    "transplat_b200.parallel.forward_view_sharded, device time, max over ranks",
            "c2_shape": one_shape("C2 shape: 131072 Gaussians, 256x256, 4 views per rank", HW, VIEWS, min(args.steps, 30), 2)}
     if args.c5:

@@ -249,6 +249,17 @@ int tsplat_cov3d_forward(int32_t G, const float* scales, const float* rotations,
 int tsplat_cov3d_backward(int32_t G, const float* scales, const float* rotations, float scale_modifier,
                           const float* dL_dcov6, float* dL_dscales, float* dL_drotations, void* cuda_stream);
 
+/* The one exchange on the path (view sharding): sums a gradient slab over the GPUs of one NVSwitch domain,
+ * in place, through the switch's reduction unit (multimem.ld_reduce + multimem.st; NVLS).  Replaces the autograd sum
+ * over the `repeat`-ed Gaussian copies (decoder_splatting_cuda.py:59-62) when those copies' views live on different
+ * GPUs - with DDP the reference would all-reduce the encoder's parameter gradients instead.
+ *   multicast_slab: the MULTICAST alias of a buffer replicated on every rank (symmetric memory; cuMulticast*), 16-byte
+ *   aligned.  Pieces (at most 4, offsets and counts in floats, multiples of 4) are reduced; rank r of `world` handles the
+ *   r-th part of every piece.  num_ctas <= 0 picks the default.  The caller orders the launch between two barriers
+ *   over the ranks: every replica completely written before, every rank's launch finished before the sums are read. */
+int tsplat_nvls_all_reduce(void* multicast_slab, const uint64_t* piece_offset_floats, const uint64_t* piece_count_floats,
+                           int32_t num_pieces, int32_t rank, int32_t world, int32_t num_ctas, void* cuda_stream);
+
 /* Device-side camera preparation for the batched decoder path: fills cams[N]
  * from what DecoderSplattingCUDA.forward receives, in one launch and with no host synchronisation.
  * Replaces the host arithmetic of render_cuda / render_depth_cuda:

@@ -25,7 +25,7 @@ DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "lo
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
            "tsplat_backward", "tsplat_mark_visible", "tsplat_pack_cameras", "tsplat_status_read", "tsplat_profile_enable",
            "tsplat_profile_read", "tsplat_adapter_forward", "tsplat_adapter_backward", "tsplat_forward_mse",
-           "tsplat_backward_mse", "tsplat_cov3d_forward", "tsplat_cov3d_backward")
+           "tsplat_backward_mse", "tsplat_cov3d_forward", "tsplat_cov3d_backward", "tsplat_nvls_all_reduce")
 
 
 class TsplatProblem(C.Structure):
@@ -96,6 +96,8 @@ def lib():
                                           C.c_void_p, C.c_void_p, C.POINTER(TsplatMse), C.c_void_p]
         L.tsplat_adapter_forward.argtypes = [C.c_void_p] * 7
         L.tsplat_adapter_backward.argtypes = [C.c_void_p] * 8
+        L.tsplat_nvls_all_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
+                                             C.c_int32, C.c_void_p]
         L.tsplat_cov3d_forward.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
         L.tsplat_cov3d_backward.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p,
                                             C.c_void_p, C.c_void_p]

@@ -10,7 +10,12 @@
     - fused (``fused_reduce=True``): the kernel that PRODUCES the gradients (preprocess_backward) adds them with
       ``multimem.red.add.f32`` through the multicast alias of a symmetric slab (torch symmetric memory, NVLS): the
       NVSwitch reduces every value into every rank's replica while the kernel is still computing, so the reduction
-      overlaps the math and no collective follows - only a barrier.
+      overlaps the math and no collective follows - only a barrier.  Exact, but every GPU receives `world` slabs:
+      slower than the all-reduce already at 2 GPUs (measured), kept as an option.
+    - two-shot NVLS (``nvls_reduce=True``, optionally with ``overlap_chunks``): the kernels write this rank's replica of
+      a symmetric slab with ordinary stores; our own kernel (csrc/exchange.cu: multimem.ld_reduce + multimem.st) then
+      sums the replicas in place through the switch, (1 + 1/world) slabs per GPU link and direction; with chunks, the
+      exchange of one Gaussian range runs on a side stream under the per-Gaussian kernel of the next.
 """
 from __future__ import annotations
 
@@ -62,6 +67,35 @@ class SymmetricGradSlab:
 
     def end_step(self):
         self.hdls[self.i].barrier(channel=1)
+
+    # ---- the two-shot exchange (csrc/exchange.cu): replicas written locally, summed through the switch afterwards ----
+    def next_replica(self):
+        """The replica this step's kernels write with ordinary stores (not cleared: they write every value)."""
+        self.i ^= 1
+        return self.bufs[self.i]
+
+    def barrier(self, channel=0):
+        self.hdls[self.i].barrier(channel=channel)
+
+    def all_reduce(self, pieces, num_ctas=0):
+        """Enqueue the in-place sum of `pieces` [(offset, count) in floats, multiples of 4, at most 4] of the current
+        replica over the ranks, on the current stream.  The caller places barriers before and after."""
+        import ctypes as C
+        from . import _lib
+        h = self.hdls[self.i]
+        n = len(pieces)
+        offs = (C.c_uint64 * 4)(*[int(o) for o, _ in pieces])
+        cnts = (C.c_uint64 * 4)(*[int(c) for _, c in pieces])
+        _lib.check(_lib.lib().tsplat_nvls_all_reduce(C.c_void_p(int(h.multicast_ptr)), offs, cnts, n, int(h.rank),
+                                                     int(h.world_size), int(num_ctas),
+                                                     C.c_void_p(torch.cuda.current_stream().cuda_stream)),
+                   "tsplat_nvls_all_reduce")
+
+    @property
+    def side_stream(self):
+        if not hasattr(self, "_side"):
+            self._side = torch.cuda.Stream(device=self.bufs[0].device)
+        return self._side
 
 
 def shard_indices(n: int, rank: int, world: int) -> list:
@@ -115,26 +149,36 @@ def replicate_with_summed_grads(gaussians: Gaussians, group=None) -> Gaussians:
 
 def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
                          depth_mode: Optional[str] = None, group=None, overlap_chunks: int = 0,
-                         fused_reduce: bool = False) -> tuple:
+                         fused_reduce: bool = False, nvls_reduce: bool = False, nvls_ctas: int = 0) -> tuple:
     """Each rank renders views rank, rank+N, ... of every scene in the batch.  Returns
     (DecoderOutput for the local views, list of the global view indices rendered here).  Backward
     through the output all-reduces the per-Gaussian gradients once - or, with ``overlap_chunks`` > 1 (one scene per
     call, CUDA decoder), range by range inside the rasterizer's backward, each all-reduce running under the kernels of
     the next Gaussian range (713 MB at C5); with ``fused_reduce`` the
-    per-Gaussian kernel itself reduces them through NVLS multicast memory (SymmetricGradSlab)."""
+    per-Gaussian kernel itself reduces them through NVLS multicast memory (SymmetricGradSlab); with ``nvls_reduce`` the
+    kernels write this rank's replica and csrc/exchange.cu sums the replicas through the switch (``overlap_chunks`` > 1:
+    range by range on a side stream, under the per-Gaussian kernel of the next range; ``nvls_ctas``: its grid)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     v = extrinsics.shape[1]
     mine = shard_indices(v, rank, world)
     staged = world > 1 and overlap_chunks > 1 and gaussians.means.shape[0] == 1 and gaussians.means.is_cuda
     fused = world > 1 and fused_reduce and gaussians.means.is_cuda
-    if world > 1 and not staged and not fused:
+    nvls = world > 1 and nvls_reduce and not fused and gaussians.means.is_cuda
+    if nvls:
+        staged = False
+    if world > 1 and not staged and not fused and not nvls:
         gaussians = replicate_with_summed_grads(gaussians, group)
     if not mine:
         # a rank without views would skip backward and leave the others waiting in the all-reduce
         raise ValueError(f"view sharding needs at least one view per rank (views={v}, ranks={world})")
     idx = torch.tensor(mine, device=extrinsics.device)
-    extra = {"grad_reduce": (group, "multimem")} if fused else ({"grad_reduce": (group, int(overlap_chunks))} if staged else {})
+    if nvls:
+        extra = {"grad_reduce": (group, "nvls", int(overlap_chunks), int(nvls_ctas))}
+    elif fused:
+        extra = {"grad_reduce": (group, "multimem")}
+    else:
+        extra = {"grad_reduce": (group, int(overlap_chunks))} if staged else {}
     out = decoder.forward(gaussians, extrinsics[:, idx], intrinsics[:, idx], near[:, idx], far[:, idx], image_shape,
                           depth_mode=depth_mode, **extra)
     return out, mine

@@ -115,6 +115,8 @@ class RenderConfig:
     sort: str | None = None    # None -> TSPLAT_SORT env ("bucket" default) | "bucket" | "onesweep"
     # view sharding (parallel.py): (process group, chunks) - the backward sums the per-Gaussian gradients over the group
     # itself, one Gaussian range at a time, each all-reduce overlapping the next range's kernels - or
+    # (process group, "nvls", chunks, ctas) - the kernels write a symmetric slab, csrc/exchange.cu sums the replicas
+    # through the switch (two-shot: multimem.ld_reduce + multimem.st), range by range under the next range's kernel;
     # (process group, "multimem") - the per-Gaussian kernel adds its values with multimem.red into a symmetric slab
     # replicated on every GPU of the NVSwitch domain (parallel.SymmetricGradSlab): no separate collective
     grad_reduce: tuple | None = None
@@ -308,10 +310,12 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
             offs.append(offs[-1] + _pad64(n_))
         reduce = cfg.grad_reduce
         multimem = reduce is not None and reduce[1] == "multimem"
-        if multimem:
+        nvls = reduce is not None and reduce[1] == "nvls"
+        if multimem or nvls:
             from .parallel import SymmetricGradSlab
-            sym = SymmetricGradSlab.get(reduce[0], dev, offs[-1] + sizes[-1])
-            slab = sym.begin_step()  # this rank's replica, zeroed; every rank has zeroed its own before anyone adds
+            sym = SymmetricGradSlab.get(reduce[0], dev, offs[-1] + _pad64(sizes[-1]))
+            # multimem: this rank's replica, zeroed; every rank has zeroed its own before anyone adds
+            slab = sym.begin_step() if multimem else sym.next_replica()
         else:
             slab = torch.empty(offs[-1] + sizes[-1], dtype=torch.float32, device=dev)
         g_means, g_cov, g_sh, g_op = (slab[o:o + n_].view(t.shape)
@@ -354,6 +358,10 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
             finally:
                 state.problem.flags = base_flags
             sym.end_step()  # every rank's kernel has finished: the replicas hold the sums over all ranks' views
+        elif nvls:
+            if g_m2d is not None:
+                raise RuntimeError("grad_reduce='nvls' does not cover the screen-space gradient (level 1 only)")
+            _backward_nvls(state, launch, sym, stream, offs, sizes, means, int(reduce[2]), int(reduce[3]))
         elif reduce is None or means.shape[0] != 1:
             launch()
             if reduce is not None:  # several scenes per call: their Gaussian ranges are not contiguous in the slab
@@ -388,6 +396,44 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
                 for w in works:
                     w.wait()
     return g_means, g_cov, g_sh, g_op, g_m2d
+
+
+def _backward_nvls(state, launch, sym, stream, offs, sizes, means, chunks, num_ctas):
+    """View sharding, two-shot exchange through the switch (parallel.py, csrc/exchange.cu): the kernels have written / write
+    this rank's replica of the symmetric slab; rank r then sums the r-th part of every piece over all replicas and stores
+    the sums into all of them.  With chunks > 1 (one scene per call) the per-Gaussian stage runs range by range and the
+    exchange of a finished range runs on a side stream under the kernel of the next range."""
+    up4 = lambda n: (n + 3) & ~3  # whole 16-byte units: a piece may run into its segment's padding
+    G = means.shape[1]
+    if chunks <= 1 or means.shape[0] != 1:
+        launch()
+        sym.barrier(0)  # every rank's replica is complete
+        sym.all_reduce([(o, up4(n)) for o, n in zip(offs, sizes)], num_ctas)
+        sym.barrier(0)  # every rank's part is stored everywhere
+        return
+    per = -(-G // chunks)
+    step = -(-per // 64) * 64  # ranges start at multiples of 64 (the per-Gaussian kernel's CTA; 16-byte units too)
+    per_g = [n // G for n in sizes]  # floats per Gaussian in each of the four pieces
+    side = sym.side_stream
+    base_flags = state.problem.flags
+    try:
+        state.problem.flags = base_flags | _lib.FLAG_BWD_RENDER_ONLY
+        launch()
+        for g0 in range(0, G, step):
+            g1 = min(G, g0 + step)
+            state.problem.flags = (base_flags | _lib.FLAG_BWD_GAUSSIANS_ONLY) & ~_lib.FLAG_REZERO_GRAD_ACC
+            state.problem.g_begin, state.problem.g_count = g0, g1 - g0
+            launch()
+            side.wait_stream(stream)
+            with torch.cuda.stream(side):
+                sym.barrier(0)  # this range is complete on every rank (and the previous range's exchange has ended)
+                sym.all_reduce([(o + g0 * k, up4((g1 - g0) * k)) for o, k in zip(offs, per_g)], num_ctas)
+        with torch.cuda.stream(side):
+            sym.barrier(0)
+        stream.wait_stream(side)
+    finally:  # the problem record is reused by a repeated backward over the same forward state
+        state.problem.flags = base_flags
+        state.problem.g_begin = state.problem.g_count = 0
 
 
 class _Rasterize(torch.autograd.Function):
