@@ -45,6 +45,12 @@ constexpr int kBwdUnroll = TSPLAT_BWD_UNROLL;
 #ifndef TSPLAT_BWD_MIN_BLOCKS
 #define TSPLAT_BWD_MIN_BLOCKS 4
 #endif
+#ifndef TSPLAT_BWD_TWOPASS
+#define TSPLAT_BWD_TWOPASS 1  // render_backward2_kernel (entry-per-lane accumulation) instead of the butterfly kernel
+#endif
+#ifndef TSPLAT_BWD2_MIN_BLOCKS
+#define TSPLAT_BWD2_MIN_BLOCKS 2
+#endif
 
 struct WarpSmem {
   float4 rec[kRenderWarps][2][kWBatch * kRecFloat4];  // the batch being composited / the one stored next
@@ -691,13 +697,242 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// render_backward, two passes per batch (the default).  The butterfly above costs 37 of a visit's 95 instructions
+// because every (warp, entry) visit reduces its 10 sums over the 32 PIXEL lanes.  Here the warp changes its lane
+// mapping in the middle of a batch instead:
+//   pass 1, lane = pixel: the sequential part - alpha, the transmittance and suffix recurrences, dL/dalpha - for the
+//     batch's entries back to front; per (entry, pixel) only two numbers leave: v = G dL/dalpha and w = alpha T, stored
+//     into a [entry][pixel] matrix in shared memory (row stride 33 float2: both passes conflict-free);
+//   pass 2, lane = ENTRY: lane k reads row k of the matrix, its own record (centre, opacity, id) and the block's 32
+//     dL/dpixel vectors (broadcast reads), and accumulates its Gaussian's 10 sums over the pixels in its own registers:
+//     no cross-lane reduction at all.  Three vector red.global.add per lane and batch deliver them.
+// Per visit: ~47 (pass 1) + 16 (pass 2) instructions instead of 111.  kBwdRows = 16 halves the matrix (more resident
+// warps): lane = (entry, half of the pixels), one shuffle per sum joins the halves.
+// ---------------------------------------------------------------------------------------------
+#ifndef TSPLAT_BWD_ROWS
+#define TSPLAT_BWD_ROWS 32
+#endif
+constexpr int kBwdRows = TSPLAT_BWD_ROWS;          // entries per pass-1 / pass-2 round: 32 or 16
+constexpr int kBwdParts = 32 / kBwdRows;           // lanes per entry in pass 2
+constexpr int kBwdPixPerPart = 32 / kBwdParts;     // pixels each of them sums
+constexpr int kMatRowBytes = 33 * 8;
+
+struct BwdSmem {
+  WarpSmem w;
+  float2 mat[kRenderWarps][kBwdRows][33];
+  float4 dl[kRenderWarps][32];
+};
+
+__device__ __forceinline__ void sts_f2(uint32_t a, float x, float y) {
+  asm volatile("st.shared.v2.f32 [%0], {%1, %2};" ::"r"(a), "f"(x), "f"(y) : "memory");
+}
+__device__ __forceinline__ float2 lds_f2(uint32_t a) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float lds_f1(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void red_global_add_v4(float* addr, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+__device__ __forceinline__ void red_global_add_v2(float* addr, float a, float b) {
+  asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(addr), "f"(a), "f"(b) : "memory");
+}
+
+template <int CH>
+__global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD2_MIN_BLOCKS) render_backward2_kernel(
+    Workspace ws, int H, int W, int G, const TsplatCamera* __restrict__ cams, const float* __restrict__ dL_dcolor,
+    const float* __restrict__ dL_ddepth, TsplatMse mse) {
+  extern __shared__ __align__(128) unsigned char bwd_smem_raw[];
+  BwdSmem& sm = *reinterpret_cast<BwdSmem*>(bwd_smem_raw);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  Stream s = make_stream(sm.w, warp, lane);
+  const size_t P = (size_t)H * W;
+  const uint32_t mat_addr = smem_u32(&sm.mat[warp][0][0]);
+  const uint32_t dl_addr = smem_u32(&sm.dl[warp][0]);
+  // pass 2: this lane's entry of the round and its share of the block's pixels
+  const int row = lane & (kBwdRows - 1), part = lane / kBwdRows;
+  const uint32_t my_row = mat_addr + (uint32_t)(row * kMatRowBytes + part * kBwdPixPerPart * 8);
+  const uint32_t my_dl = dl_addr + (uint32_t)(part * kBwdPixPerPart * 16);
+
+  // work units: list segments (emitted by render_forward), dealt round-robin: all full segments (equal work) first, then
+  // the partial ones
+  const unsigned int nfull_all = ws.ctl->seg_full, nseg = nfull_all + ws.ctl->seg_part;
+  const unsigned int W_all = gridDim.x * kRenderWarps, gw = blockIdx.x * kRenderWarps + warp;
+  auto load_seg = [&](unsigned int idx, unsigned int& list_start, unsigned int& list_len, unsigned int& k) {
+    JobRec r{0u, 0u, 0u};
+    list_start = 0u; list_len = 0u; k = 0u;
+    if (idx < nseg) {
+      const uint4 q = __ldcg(ws.segs + (idx < nfull_all ? idx : ws.seg_cap - 1 - (idx - nfull_all)));
+      list_start = q.x; list_len = q.y; k = q.w;
+      r.start = q.x + q.w * kSegLen;
+      r.count = min((unsigned int)kSegLen, q.y - q.w * kSegLen);
+      r.id = q.z;
+    }
+    return r;
+  };
+  unsigned int cur_ls, cur_ll, cur_k, nxt_ls, nxt_ll, nxt_k;
+  JobRec cur = load_seg(gw, cur_ls, cur_ll, cur_k), nxt = load_seg(gw + W_all, nxt_ls, nxt_ll, nxt_k);
+  for (unsigned int idx = gw; idx < nseg; idx += W_all) {
+    unsigned int fut_ls, fut_ll, fut_k;
+    const JobRec fut = load_seg(idx + 2 * W_all, fut_ls, fut_ll, fut_k);  // in flight while this unit runs
+    pump<true>(s, cur, nxt, ws.bref, lane);
+    const int count = (int)cur.count;  // > 0 by construction
+    {
+      const int blk = (int)(cur.id & 7u);
+      const int bid = (int)(cur.id >> 3);
+      const int n = bid / ws.T, tile = bid - n * ws.T;
+      const int ty = tile / ws.tiles_x, tx = tile - ty * ws.tiles_x;
+      int px, py;
+      pixel_of_lane(blk, lane, tx, ty, px, py);
+      const bool inside = px < W && py < H;
+      const float pxf = (float)px, pyf = (float)py;
+      const size_t pix = (size_t)py * W + px;
+      // origin of this lane's pixels in pass 2 (pixel p of the block = column p & 7, row p >> 3)
+      const float ox = (float)(px - (lane & 7)), oy = (float)(py - (lane >> 3) + part * (kBwdPixPerPart / 8));
+
+      const float T_final = inside ? ws.final_T[n * P + pix] : 0.0f;
+      float T = T_final;
+      const unsigned int last_contributor = inside ? ws.n_contrib[n * P + pix] : 0u;
+      const unsigned int hi = cur_k * kSegLen + (unsigned int)count;
+      const bool restart = hi < cur_ll;  // see render_backward_kernel
+      TS_CHECK(!restart || (size_t)(cur_ls / kSegLen) + hi / kSegLen < ws.e_cap / kSegLen + 2);
+      const float* ck = ws.ckpt + ((size_t)(cur_ls / kSegLen) + hi / kSegLen) * kCkptFloats + lane;
+      float dL_dpix[4] = {0.0f, 0.0f, 0.0f, 0.0f};
+      float accum_dl = 0.0f, w_last = 0.0f, oml_last = 1.0f;
+      if (inside) {
+        if (dL_dcolor != nullptr) {
+#pragma unroll
+          for (int ch = 0; ch < 3; ch++) dL_dpix[ch] = dL_dcolor[(n * 3 + ch) * P + pix];
+        }
+        if (mse.target != nullptr) {  // fused MSE: dL/dcolor += dL/dloss * 2 w / numel * (colour - target)
+          const float gl = __ldg(mse.dL_dloss) * mse.scale;
+#pragma unroll
+          for (int ch = 0; ch < 3; ch++)
+            dL_dpix[ch] += gl * (mse.color[(n * 3 + ch) * P + pix] - mse.target[(n * 3 + ch) * P + pix]);
+        }
+        if (CH == 4) dL_dpix[3] = dL_ddepth[n * P + pix];
+        if (restart) {
+          const float Tc = ck[0];
+          const float* cf = ws.c_final + (size_t)n * 4 * P + pix;
+          float a = 0.0f;
+#pragma unroll
+          for (int ch = 0; ch < CH; ch++) a += dL_dpix[ch] * (cf[(size_t)ch * P] - ck[32 * (ch + 1)]);
+          accum_dl = a * rcp_hot(Tc);
+          T = Tc;
+        }
+      }
+      __syncwarp();  // the previous unit's pass 2 has read dl
+      sts_f4(dl_addr + (uint32_t)lane * 16u, make_float4(dL_dpix[0], dL_dpix[1], dL_dpix[2], dL_dpix[3]));
+      const float* bgp = cams[n].bg;
+      // bg of the fused depth channel is 0 (render_depth_cuda passes zeros, cuda_splatting.py:410)
+      const float bg_dot = __ldg(bgp) * dL_dpix[0] + __ldg(bgp + 1) * dL_dpix[1] + __ldg(bgp + 2) * dL_dpix[2];
+      const float bgT = -T_final * bg_dot;
+      float* const acc_view = ws.grad_acc + (size_t)n * G * kAccFloats;
+
+      // batch b (b = 0 is the END of the list) is chunk nb - 1 - b of the block list
+      const int nb = batches_of(cur);
+      for (int b = 0; b < nb; b++) {
+        const int cnt = batch_cnt<true>(cur, b);
+        const uint32_t base = stage_batch<true>(s, ws, G, cur, nxt, b, lane);
+        for (int k_hi = cnt; k_hi > 0; k_hi -= kBwdRows) {
+          const int k_lo = k_hi > kBwdRows ? k_hi - kBwdRows : 0;
+          // ---- pass 1: lane = pixel ----
+          unsigned int rowmask = 0u;
+          uint32_t rk = base + (uint32_t)((k_hi - 1) * kRecBytes);
+          uint32_t mk = mat_addr + (uint32_t)((k_hi - 1 - k_lo) * kMatRowBytes + lane * 8);
+#pragma unroll kBwdUnroll
+          for (int k = k_hi - 1; k >= k_lo; k--, rk -= kRecBytes, mk -= kMatRowBytes) {
+            const float4 a0 = lds_f4(rk);
+            const float4 a1 = lds_f4(rk + 16u);
+            const float4 a2 = lds_f4(rk + 32u);
+            const float dx = a0.x - pxf, dy = a0.y - pyf;
+            const float power = -0.5f * (a0.z * dx * dx + a1.x * dy * dy) - a0.w * dx * dy;
+            const float Gv = exp_hot(power);
+            const float alpha = fminf(0.99f, a1.y * Gv);
+            // entries behind this pixel's last contributor are skipped (tile-list positions, 1-based)
+            const bool valid = (__float_as_uint(a2.w) <= last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+            if (!__any_sync(0xffffffffu, valid)) continue;
+            rowmask |= 1u << (k - k_lo);
+            // no branch on `valid`: a lane that does not contribute runs the same arithmetic with alpha = 0
+            const float Gm = valid ? Gv : 0.0f, am = valid ? alpha : 0.0f;
+            const float col[4] = {a1.z, a1.w, a2.x, a2.y};
+            const float oma = 1.0f - am;
+            const float inv1ma = rcp_hot(oma);
+            const float Tn = T * inv1ma;
+            float cdl = 0.0f;
+#pragma unroll
+            for (int ch = 0; ch < CH; ch++) cdl += col[ch] * dL_dpix[ch];
+            const float acc_new = w_last + oml_last * accum_dl;
+            const float dL_dalpha = (cdl - acc_new) * Tn + bgT * inv1ma;
+            T = Tn; accum_dl = acc_new; w_last = am * cdl; oml_last = oma;
+            sts_f2(mk, Gm * dL_dalpha, am * Tn);
+          }
+          __syncwarp();
+          // ---- pass 2: lane = entry (x part of the pixels) ----
+          if (rowmask != 0u) {
+            const uint32_t rr = base + (uint32_t)((k_lo + row) * kRecBytes);
+            const float2 cxy = lds_f2(rr);
+            const float opac = lds_f1(rr + 20u);
+            const unsigned int gid = __float_as_uint(lds_f1(rr + 40u));
+            const float gx = cxy.x - ox, gy = cxy.y - oy;
+            float Sx = 0.f, Sy = 0.f, Sxx = 0.f, Sxy = 0.f, Syy = 0.f, Sop = 0.f, C0 = 0.f, C1 = 0.f, C2 = 0.f, C3 = 0.f;
+            float dxc[8];
+#pragma unroll
+            for (int c = 0; c < 8; c++) dxc[c] = gx - (float)c;
+#pragma unroll
+            for (int i = 0; i < kBwdPixPerPart; i++) {
+              const float2 vw = lds_f2(my_row + (uint32_t)i * 8u);
+              const float4 dl = lds_f4(my_dl + (uint32_t)i * 16u);
+              const float dx = dxc[i & 7], dy = gy - (float)(i >> 3);
+              const float u = opac * vw.x;
+              const float ux = u * dx, uy = u * dy;
+              Sx += ux; Sy += uy;
+              Sxx += ux * dx; Sxy += ux * dy; Syy += uy * dy;
+              Sop += vw.x;
+              C0 += vw.y * dl.x; C1 += vw.y * dl.y; C2 += vw.y * dl.z;
+              if (CH == 4) C3 += vw.y * dl.w;
+            }
+            if (kBwdParts == 2) {
+              const unsigned int full = 0xffffffffu;
+              Sx += __shfl_xor_sync(full, Sx, 16); Sy += __shfl_xor_sync(full, Sy, 16);
+              Sxx += __shfl_xor_sync(full, Sxx, 16); Sxy += __shfl_xor_sync(full, Sxy, 16);
+              Syy += __shfl_xor_sync(full, Syy, 16); Sop += __shfl_xor_sync(full, Sop, 16);
+              C0 += __shfl_xor_sync(full, C0, 16); C1 += __shfl_xor_sync(full, C1, 16);
+              C2 += __shfl_xor_sync(full, C2, 16);
+              if (CH == 4) C3 += __shfl_xor_sync(full, C3, 16);
+            }
+            if (part == 0 && ((rowmask >> row) & 1u)) {
+              TS_CHECK(gid < (unsigned int)G);
+              float* acc = acc_view + (size_t)gid * kAccFloats;
+              red_global_add_v4(acc, Sx, Sy, Sxx, Sxy);
+              red_global_add_v4(acc + 4, Syy, Sop, C0, C1);
+              if (CH == 4) red_global_add_v2(acc + 8, C2, C3);
+              else red_global_add(acc + 8, C2);
+            }
+          }
+          __syncwarp();  // the next round's pass 1 rewrites the matrix
+        }
+      }
+    }
+    advance_job(s, cur, nxt, fut);
+    cur_ls = nxt_ls; cur_ll = nxt_ll; cur_k = nxt_k;
+    nxt_ls = fut_ls; nxt_ll = fut_ll; nxt_k = fut_k;
+  }
+}
+
 // persistent grids: resident CTAs per SM x SMs of the device, queried once per kernel
 template <class K>
-static int persistent_grid(K kernel) {
+static int persistent_grid(K kernel, int dyn_smem = 0) {
   int dev = 0, sms = 148, per_sm = 1;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kRenderThreads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kRenderThreads, dyn_smem) != cudaSuccess || per_sm < 1) per_sm = 1;
 #ifdef TSPLAT_RENDER_CTAS_PER_SM
   if (per_sm > TSPLAT_RENDER_CTAS_PER_SM) per_sm = TSPLAT_RENDER_CTAS_PER_SM;
 #endif
@@ -730,6 +965,20 @@ cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, 
   TsplatMse mse{};
   if (mse_in) mse = *mse_in;
   const int cap = (njobs + kRenderWarps - 1) / kRenderWarps;
+#if TSPLAT_BWD_TWOPASS
+  const int smem = (int)sizeof(BwdSmem);
+  if (p.depth_mode != TSPLAT_DEPTH_NONE) {
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(render_backward2_kernel<4>), smem);
+    if (e != cudaSuccess) return e;
+    static const int per = persistent_grid(render_backward2_kernel<4>, smem);
+    render_backward2_kernel<4><<<min(per, cap), kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth, mse);
+  } else {
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(render_backward2_kernel<3>), smem);
+    if (e != cudaSuccess) return e;
+    static const int per = persistent_grid(render_backward2_kernel<3>, smem);
+    render_backward2_kernel<3><<<min(per, cap), kRenderThreads, smem, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth, mse);
+  }
+#else
   if (p.depth_mode != TSPLAT_DEPTH_NONE) {
     static const int per = persistent_grid(render_backward_kernel<4>);
     render_backward_kernel<4><<<min(per, cap), kRenderThreads, 0, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth, mse);
@@ -737,6 +986,7 @@ cudaError_t launch_render_backward(const TsplatProblem& p, const Workspace& ws, 
     static const int per = persistent_grid(render_backward_kernel<3>);
     render_backward_kernel<3><<<min(per, cap), kRenderThreads, 0, st>>>(ws, p.H, p.W, p.G, p.cams, dL_dcolor, dL_ddepth, mse);
   }
+#endif
   return cudaGetLastError();
 }
 
