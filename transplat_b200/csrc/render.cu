@@ -46,7 +46,7 @@ constexpr int kBwdUnroll = TSPLAT_BWD_UNROLL;
 #define TSPLAT_BWD_MIN_BLOCKS 4
 #endif
 #ifndef TSPLAT_BWD_TWOPASS
-#define TSPLAT_BWD_TWOPASS 1  // render_backward2_kernel (entry-per-lane accumulation) instead of the butterfly kernel
+#define TSPLAT_BWD_TWOPASS 0  // 1: render_backward2_kernel (entry-per-lane accumulation) instead of the butterfly kernel
 #endif
 #ifndef TSPLAT_BWD2_MIN_BLOCKS
 #define TSPLAT_BWD2_MIN_BLOCKS 2
