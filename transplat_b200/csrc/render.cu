@@ -46,10 +46,13 @@ constexpr int kBwdUnroll = TSPLAT_BWD_UNROLL;
 #define TSPLAT_BWD_MIN_BLOCKS 4
 #endif
 #ifndef TSPLAT_BWD_TWOPASS
-#define TSPLAT_BWD_TWOPASS 0  // 1: render_backward2_kernel (entry-per-lane accumulation) instead of the butterfly kernel
+#define TSPLAT_BWD_TWOPASS 1  // render_backward2_kernel (entry-per-lane accumulation) instead of the butterfly kernel
 #endif
 #ifndef TSPLAT_BWD2_MIN_BLOCKS
-#define TSPLAT_BWD2_MIN_BLOCKS 2
+#define TSPLAT_BWD2_MIN_BLOCKS 3  // 16-row matrix: 71 KB of shared memory per CTA, 80 registers
+#endif
+#ifndef TSPLAT_BWD2_UNROLL
+#define TSPLAT_BWD2_UNROLL 2
 #endif
 
 struct WarpSmem {
@@ -711,8 +714,9 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD_MIN_BLOCKS) render_
 // warps): lane = (entry, half of the pixels), one shuffle per sum joins the halves.
 // ---------------------------------------------------------------------------------------------
 #ifndef TSPLAT_BWD_ROWS
-#define TSPLAT_BWD_ROWS 32
+#define TSPLAT_BWD_ROWS 16  // C2, render_backward: 32 rows (2 CTAs per SM) 0.1946 / 0.1935 ms at unroll 1 / 2; 16 rows (3 CTAs) 0.1935 / 0.1919
 #endif
+constexpr int kBwd2Unroll = TSPLAT_BWD2_UNROLL;    // pass-1 visits in flight
 constexpr int kBwdRows = TSPLAT_BWD_ROWS;          // entries per pass-1 / pass-2 round: 32 or 16
 constexpr int kBwdParts = 32 / kBwdRows;           // lanes per entry in pass 2
 constexpr int kBwdPixPerPart = 32 / kBwdParts;     // pixels each of them sums
@@ -846,7 +850,7 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD2_MIN_BLOCKS) render
           unsigned int rowmask = 0u;
           uint32_t rk = base + (uint32_t)((k_hi - 1) * kRecBytes);
           uint32_t mk = mat_addr + (uint32_t)((k_hi - 1 - k_lo) * kMatRowBytes + lane * 8);
-#pragma unroll kBwdUnroll
+#pragma unroll kBwd2Unroll
           for (int k = k_hi - 1; k >= k_lo; k--, rk -= kRecBytes, mk -= kMatRowBytes) {
             const float4 a0 = lds_f4(rk);
             const float4 a1 = lds_f4(rk + 16u);
