@@ -60,6 +60,7 @@ __device__ __forceinline__ void count_tiles(unsigned int* __restrict__ cnt, int 
 #ifndef TSPLAT_PRE_MIN_BLOCKS
 #define TSPLAT_PRE_MIN_BLOCKS 4  // 64 registers: 8 CTAs of 4 warps per SM (3 -> 80 registers, 39.6 us; 4 -> 37.3 us at C2)
 #endif
+template <int LAYOUT>
 __global__ void __launch_bounds__(kPreG * kPreMaxWarps, TSPLAT_PRE_MIN_BLOCKS) preprocess_forward_kernel(PreArgs a, Workspace ws, int* out_radii) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
@@ -180,7 +181,7 @@ __global__ void __launch_bounds__(kPreG * kPreMaxWarps, TSPLAT_PRE_MIN_BLOCKS) p
             for (int k = 0; k < 25; k++) {
               if (k < nb) {
 #pragma unroll
-                for (int ch = 0; ch < 3; ch++) acc[ch] += bs[k] * my_sh[sh_idx(p.sh_layout, M, k, ch)];
+                for (int ch = 0; ch < 3; ch++) acc[ch] += bs[k] * my_sh[sh_idx(LAYOUT, M, k, ch)];
               }
             }
 #pragma unroll
@@ -250,12 +251,15 @@ cudaError_t launch_preprocess(const TsplatProblem& p, const Workspace& ws, int* 
   a.bulk_ok = al16(p.means) && al16(p.cov) && al16(p.sh) && al16(p.opacity) && stride_ok &&
               ((kPreG * 4 * a.sh_floats) % 16 == 0);
   const size_t smem = 16 + sizeof(float) * kPreG * (1 + 3 + a.cov_floats + a.sh_floats);
-  cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(preprocess_forward_kernel), (int)smem);
-  if (e != cudaSuccess) return e;
   dim3 grid((p.G + kPreG - 1) / kPreG, p.B);
   const int warps = p.V < kPreMaxWarps ? p.V : kPreMaxWarps;
-  preprocess_forward_kernel<<<grid, 32 * warps, smem, st>>>(a, ws, out_radii);
-  return cudaGetLastError();
+  auto go = [&](auto kernel) -> cudaError_t {
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(kernel), (int)smem);
+    if (e != cudaSuccess) return e;
+    kernel<<<grid, 32 * warps, smem, st>>>(a, ws, out_radii);
+    return cudaGetLastError();
+  };
+  return p.sh_layout == TSPLAT_SH_GM3 ? go(preprocess_forward_kernel<TSPLAT_SH_GM3>) : go(preprocess_forward_kernel<TSPLAT_SH_G3M>);
 }
 
 cudaError_t launch_mark_visible(int G, const float* means, const float* view, uint8_t* present, cudaStream_t st) {

@@ -8,9 +8,9 @@
 //   phase A  thread (Gaussian, view): cov2D / projection / depth-feature backward in registers; the SH part leaves the
 //            view's 25 basis values and 3 masked colour gradients in shared memory and accumulates dL/d(direction) on the
 //            fly (no 25 x 3 derivative table in registers: round 1 needed 167 registers and ran at 14 % occupancy);
-//   phase B  the CTA's 32 x 75 dL/dsh values, a contiguous run of 19 (10) per thread: sum over views of basis x colour
-//            gradient in registers (no shared-memory read-modify-write per view), staged once and written to HBM
-//            with one bulk store per CTA;
+//   phase B  the CTA's 32 x 75 dL/dsh values: a warp per channel (and half of the coefficients), a lane per Gaussian: sum
+//            over views of basis x colour gradient in registers (no shared-memory read-modify-write per view), staged
+//            once and written to HBM with one bulk store per CTA;
 //   phase C  the 10 remaining per-Gaussian sums (mean 3, covariance 6, opacity 1) over the views through shared memory.
 // HBM-bound: reads 340 + V (48 + 5) B, writes 340 B per Gaussian.
 #include "geom.cuh"
@@ -117,7 +117,7 @@ __device__ __forceinline__ int sh_basis_backward(int deg, int sh_l4, float x, fl
 #endif
 // NW warps per CTA (4 or 8: at least 4 even for fewer views, so that phase B's 2400 outputs are at most 19 per thread and
 // stay in registers)
-template <int NW>
+template <int NW, int LAYOUT>
 __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) preprocess_backward_kernel(PreBwdArgs a, Workspace ws) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
@@ -175,15 +175,21 @@ __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) pre
   const float* my_sh = s_sh + (size_t)lane * a.sh_floats;
   float* my_scr = s_scr + ((size_t)warp * kBwdG + lane) * kScr;
 
-  // phase B's outputs: thread t owns Gaussian t / TPG of the CTA and a contiguous run of kMaxOut of its sh_floats
-  // dL/dsh values (the layout of p.sh), so that (coefficient, channel) advance by increments - no division per output
-  constexpr int TPG = nthreads / kBwdG;                 // threads per Gaussian: 4 or 8
-  constexpr int kMaxOut = (75 + TPG - 1) / TPG;         // 19 or 10
-  const int out_g = tid / TPG, out_j = tid % TPG;
-  const int out_r0 = out_j * kMaxOut;                   // first value of the run inside the Gaussian's block
-  float dsh[kMaxOut];
+  // phase B's outputs: warp w sums channel w % 3 (and, with 8 warps, half w / 3 of the coefficients) for the CTA's 32
+  // Gaussians, one per lane: the colour gradient is read once per view and every basis value feeds one FFMA; the
+  // sums stay in registers over all rounds.  Warps beyond 3 (6) have no phase-B work.
+  constexpr int kSplit = NW / 4;                        // 1 or 2
+  constexpr int kKPer = (25 + kSplit - 1) / kSplit;     // 25 or 13 coefficients per thread
+  constexpr int kShStride = LAYOUT == TSPLAT_SH_GM3 ? 3 : 1;
+  const bool b_on = warp < 3 * kSplit;
+  const int b_ch = warp % 3, b_k0 = (warp / 3) * kKPer;
+  float dsh[kKPer];
 #pragma unroll
-  for (int i = 0; i < kMaxOut; i++) dsh[i] = 0.0f;
+  for (int i = 0; i < kKPer; i++) dsh[i] = 0.0f;
+  // this lane's coefficients of the three channels (phase A): immediate offsets for every constant k
+  const float* sh_c0 = my_sh;
+  const float* sh_c1 = LAYOUT == TSPLAT_SH_GM3 ? my_sh + 1 : my_sh + M;
+  const float* sh_c2 = LAYOUT == TSPLAT_SH_GM3 ? my_sh + 2 : my_sh + 2 * M;
 
   const int rounds = (p.V + nwarps - 1) / nwarps;
   for (int r = 0; r < rounds; r++) {
@@ -288,13 +294,9 @@ __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) pre
           const float len = sqrtf(sum2);
           const float dxn = ox / len, dyn = oy / len, dzn = oz / len;
           float ddx = 0.f, ddy = 0.f, ddz = 0.f;
-          const int layout = p.sh_layout;
           nb = sh_basis_backward(
               p.sh_degree, p.sh_l4, dxn, dyn, dzn,
-              [&](int k) {
-                return my_sh[sh_idx(layout, M, k, 0)] * dc0 + my_sh[sh_idx(layout, M, k, 1)] * dc1 +
-                       my_sh[sh_idx(layout, M, k, 2)] * dc2;
-              },
+              [&](int k) { return sh_c0[k * kShStride] * dc0 + sh_c1[k * kShStride] * dc1 + sh_c2[k * kShStride] * dc2; },
               [&](int k, float val) { my_scr[k] = val; }, ddx, ddy, ddz);
           const float inv32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
           dmean[0] += ((sum2 - ox * ox) * ddx - oy * ox * ddy - oz * ox * ddz) * inv32;
@@ -325,36 +327,36 @@ __global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) pre
     for (int k = nb; k < 25; k++) my_scr[k] = 0.0f;
     my_scr[25] = dc0; my_scr[26] = dc1; my_scr[27] = dc2;
     __syncthreads();
-    // ---- phase B: dL/dsh[g][r] += sum over this round's views of basis[k(r)] * dcolour[ch(r)] ----
-    {
-      int k, ch;
-      if (M == 0) { k = 0; ch = out_r0; }
-      else if (p.sh_layout == TSPLAT_SH_GM3) { k = out_r0 / 3; ch = out_r0 - 3 * k; }
-      else { ch = out_r0 / M; k = out_r0 - ch * M; }
-      const float* sc0 = s_scr + (size_t)out_g * kScr;
+    // ---- phase B: dL/dsh[g][k][ch] += sum over this round's views of basis[k] * dcolour[ch] ----
+    if (b_on) {
+      const float* sc = s_scr + (size_t)lane * kScr;
 #pragma unroll
-      for (int i = 0; i < kMaxOut; i++) {
-        if (out_r0 + i < a.sh_floats && k < 25) {
-          float acc = 0.0f;
-          const float* sc = sc0;
+      for (int w = 0; w < nwarps; w++, sc += kBwdG * kScr) {
+        const float dc = sc[25 + b_ch];
+        if (M == 0) {
+          dsh[0] += dc;
+        } else {
 #pragma unroll
-          for (int w = 0; w < nwarps; w++, sc += kBwdG * kScr) acc += (M == 0 ? 1.0f : sc[k]) * sc[25 + ch];
-          dsh[i] += acc;
+          for (int i = 0; i < kKPer; i++)
+            if (b_k0 + i < 25) dsh[i] += sc[b_k0 + i] * dc;
         }
-        if (M == 0) ch++;
-        else if (p.sh_layout == TSPLAT_SH_GM3) { if (++ch == 3) { ch = 0; k++; } }
-        else { if (++k == M) { k = 0; ch++; } }
       }
     }
     __syncthreads();  // the scratch is rewritten by the next round
   }
   // ---- dL/dsh leaves through the (now idle) staging area of the SH inputs: one bulk store per CTA ----
   float* g_dsh = a.dL_dsh + gbase * a.sh_floats;
-  {
-    float* so = s_sh + (size_t)out_g * a.sh_floats + out_r0;
+  if (b_on) {
+    float* so = s_sh + (size_t)lane * a.sh_floats;
+    if (M == 0) {
+      if (b_k0 == 0) so[b_ch] = dsh[0];
+    } else {
 #pragma unroll
-    for (int i = 0; i < kMaxOut; i++)
-      if (out_r0 + i < a.sh_floats) so[i] = dsh[i];
+      for (int i = 0; i < kKPer; i++) {
+        const int k = b_k0 + i;
+        if (k < M && k < 25) so[LAYOUT == TSPLAT_SH_GM3 ? k * 3 + b_ch : b_ch * M + k] = dsh[i];
+      }
+    }
   }
   if (a.multimem) {
     // view sharding: this rank's sums go straight into every rank's gradient slab, reduced by the switch; Gaussians no
@@ -450,16 +452,18 @@ cudaError_t launch_preprocess_backward(const TsplatProblem& p, const Workspace& 
   const int warps = p.V <= 4 ? 4 : kBwdMaxWarps;
   const size_t smem = 16 + sizeof(float) * kBwdG * (3 + a.cov_floats + a.sh_floats + warps * (kScr + kPart));
   dim3 grid((g_count + kBwdG - 1) / kBwdG, p.B);
+  auto go = [&](auto kernel, int nw) -> cudaError_t {
+    cudaError_t e = ensure_dynamic_smem(reinterpret_cast<const void*>(kernel), (int)smem);
+    if (e != cudaSuccess) return e;
+    kernel<<<grid, 32 * nw, smem, st>>>(a, ws);
+    return cudaSuccess;
+  };
   cudaError_t e;
-  if (warps == 4) {
-    e = ensure_dynamic_smem(reinterpret_cast<const void*>(preprocess_backward_kernel<4>), (int)smem);
-    if (e != cudaSuccess) return e;
-    preprocess_backward_kernel<4><<<grid, 32 * 4, smem, st>>>(a, ws);
-  } else {
-    e = ensure_dynamic_smem(reinterpret_cast<const void*>(preprocess_backward_kernel<8>), (int)smem);
-    if (e != cudaSuccess) return e;
-    preprocess_backward_kernel<8><<<grid, 32 * 8, smem, st>>>(a, ws);
-  }
+  if (p.sh_layout == TSPLAT_SH_GM3)
+    e = warps == 4 ? go(preprocess_backward_kernel<4, TSPLAT_SH_GM3>, 4) : go(preprocess_backward_kernel<8, TSPLAT_SH_GM3>, 8);
+  else
+    e = warps == 4 ? go(preprocess_backward_kernel<4, TSPLAT_SH_G3M>, 4) : go(preprocess_backward_kernel<8, TSPLAT_SH_G3M>, 8);
+  if (e != cudaSuccess) return e;
   return cudaGetLastError();
 }
 
