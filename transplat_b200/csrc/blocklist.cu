@@ -10,10 +10,11 @@
 // touch: E = 2.2 D references at C2, which is why the lists hold references and the render warps gather the 48-B records
 // from the L2-resident per-Gaussian array themselves (copying the records E times cost 118 MB of DRAM writes per step).
 //
-// block_lists_kernel: one CTA per (view, tile).  Pass 1: per pair, the per-Gaussian record's cull inputs -> block mask
-// (cull.cuh), masks stored, per-block counts reduced; one returning atomic per tile reserves the tile's 8 lists as one
-// contiguous run of the reference buffer.  Pass 2: per chunk of pairs, ballot ranks + running per-block bases place every
-// (pair, block) reference.  The CTA of slot s of the heaviest-first tile order also writes the records of render jobs
+// block_lists_kernel: one CTA per (view, tile); each of its 16 warps owns a contiguous run of the tile list.  Pass 1:
+// per pair, the per-Gaussian record's cull inputs -> block mask (cull.cuh), masks stored, per-(warp, block) counts; one
+// exchange of those counts and one returning atomic per tile reserve the tile's 8 lists as one contiguous run of the
+// reference buffer.  Pass 2: per chunk of 32 pairs, ballot ranks + the warp's running per-block positions (registers)
+// place every (pair, block) reference - no shared memory, no CTA barrier.  The CTA of slot s of the heaviest-first tile order also writes the records of render jobs
 // 8 s .. 8 s + 7: render_forward deals them in that order (a separate counting sort of the jobs by their own list length
 // cost 10 us and bought 6).
 #include "cull.cuh"
@@ -30,11 +31,9 @@ constexpr int kBlThreads = TSPLAT_BL_THREADS;
 constexpr int kBlWarps = kBlThreads / 32;
 
 __global__ void __launch_bounds__(kBlThreads, TSPLAT_BL_MIN_BLOCKS) block_lists_kernel(Workspace ws, int G, const unsigned int* __restrict__ vals) {
-  __shared__ unsigned int s_cnt[kBlocksPerTile];               // pass 1: entries per block
   __shared__ unsigned int s_start[kBlocksPerTile];             // first entry of each block's list (clipped to e_cap)
   __shared__ unsigned int s_lim[kBlocksPerTile];               // one past its last usable entry
-  __shared__ unsigned int s_run[kBlocksPerTile];               // pass 2: entries placed by earlier chunks
-  __shared__ unsigned int s_wcnt[kBlWarps][kBlocksPerTile];    // pass 2: per-warp counts of the current chunk -> exclusive offsets
+  __shared__ unsigned int s_wcnt[kBlWarps][kBlocksPerTile];    // per-warp counts -> exclusive offsets within the block's list
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int slot = (int)blockIdx.x;                            // position in the heaviest-first order = render job order
   const int bid = ws.use_order ? (int)ws.tile_order[slot] : slot;
@@ -50,93 +49,96 @@ __global__ void __launch_bounds__(kBlThreads, TSPLAT_BL_MIN_BLOCKS) block_lists_
   const int ty = tile / ws.tiles_x, tx = tile - ty * ws.tiles_x;
   const float tileX0 = (float)(tx * kTile), tileY0 = (float)(ty * kTile);
   const float4* __restrict__ grec = ws.grec + (size_t)view * G * kRecFloat4;
-  if (tid < kBlocksPerTile) { s_cnt[tid] = 0u; s_run[tid] = 0u; }
-  __syncthreads();
+  // Warp w owns a contiguous run of 32-pair chunks of the tile list: list order = (warp, chunk, lane) order, so after
+  // one exchange of the per-warp counts the placement pass needs neither shared memory nor CTA barriers.
+  const int chunks = (n + 31) >> 5;
+  const int c_lo = (int)(((long long)chunks * warp) / kBlWarps), c_hi = (int)(((long long)chunks * (warp + 1)) / kBlWarps);
 
   // ---- pass 1: block masks and per-block counts ----
-  unsigned int c01 = 0, c23 = 0, c45 = 0, c67 = 0;  // pairs of 16-bit counters (a thread sees at most n / 1024 + 1 pairs)
-  for (int j = tid; j < n; j += kBlThreads) {
-    const unsigned int id = vals[range.x + j];
-    TS_CHECK(id < (unsigned int)G && range.x + (unsigned int)j < ws.d_cap);
-    const float4* __restrict__ gr = grec + (size_t)id * kRecFloat4;
-    const float4 g0 = gr[0];
-    const float cq = gr[1].x, tau = gr[2].w;
-    const unsigned int m = cull_block_mask(g0, cq, tau, tileX0, tileY0);
-    ws.pair_mask[range.x + j] = (unsigned char)m;
-    c01 += (m & 1u) | ((m & 2u) << 15);
-    c23 += ((m >> 2) & 1u) | ((m & 8u) << 13);
-    c45 += ((m >> 4) & 1u) | ((m & 32u) << 11);
-    c67 += ((m >> 6) & 1u) | ((m & 128u) << 9);
+  unsigned int c01 = 0, c23 = 0, c45 = 0, c67 = 0;  // pairs of 16-bit counters (a lane sees at most n / 512 + 1 pairs)
+  for (int c = c_lo; c < c_hi; c++) {
+    const int j = (c << 5) + lane;
+    if (j < n) {
+      const unsigned int id = vals[range.x + j];
+      TS_CHECK(id < (unsigned int)G && range.x + (unsigned int)j < ws.d_cap);
+      const float4* __restrict__ gr = grec + (size_t)id * kRecFloat4;
+      const float4 g0 = gr[0];
+      const float cq = gr[1].x, tau = gr[2].w;
+      const unsigned int m = cull_block_mask(g0, cq, tau, tileX0, tileY0);
+      ws.pair_mask[range.x + j] = (unsigned char)m;
+      c01 += (m & 1u) | ((m & 2u) << 15);
+      c23 += ((m >> 2) & 1u) | ((m & 8u) << 13);
+      c45 += ((m >> 4) & 1u) | ((m & 32u) << 11);
+      c67 += ((m >> 6) & 1u) | ((m & 128u) << 9);
+    }
   }
   {
-    unsigned int c[8] = {c01 & 0xffffu, c01 >> 16, c23 & 0xffffu, c23 >> 16, c45 & 0xffffu, c45 >> 16, c67 & 0xffffu, c67 >> 16};
+    const unsigned int c[8] = {c01 & 0xffffu, c01 >> 16, c23 & 0xffffu, c23 >> 16, c45 & 0xffffu, c45 >> 16, c67 & 0xffffu, c67 >> 16};
 #pragma unroll
     for (int b = 0; b < 8; b++) {
       const unsigned int t = __reduce_add_sync(0xffffffffu, c[b]);
-      if (lane == 0 && t) atomicAdd(&s_cnt[b], t);
+      if (lane == 0) s_wcnt[warp][b] = t;
     }
   }
   __syncthreads();
-  if (tid == 0) {
+  if (warp == 0) {
+    // lane b < 8: exclusive scan of block b's per-warp counts; then lane 0 reserves the tile's 8 lists as one run
+    unsigned int total_b = 0;
+    if (lane < kBlocksPerTile) {
+#pragma unroll
+      for (int w = 0; w < kBlWarps; w++) {
+        const unsigned int t = s_wcnt[w][lane];
+        s_wcnt[w][lane] = total_b;
+        total_b += t;
+      }
+    }
     // every list starts at an even reference index (16-B aligned: the render warps stream it with bulk copies)
-    unsigned int total = 0;
+    const unsigned int padded = (total_b + 1u) & ~1u;
+    unsigned int incl = padded;
 #pragma unroll
-    for (int b = 0; b < 8; b++) total += (s_cnt[b] + 1u) & ~1u;
-    const unsigned long long base = atomicAdd(&ws.ctl->num_block_entries, (unsigned long long)total);
-    if (base + total > ws.e_cap) ws.ctl->overflow = 1u;  // entries beyond the capacity are dropped, never written
-    unsigned long long off = base;
-#pragma unroll
-    for (int b = 0; b < 8; b++) {
+    for (int d = 1; d < kBlocksPerTile; d <<= 1) {
+      const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    const unsigned int total = __shfl_sync(0xffffffffu, incl, kBlocksPerTile - 1);
+    unsigned long long base = 0;
+    if (lane == 0) {
+      base = atomicAdd(&ws.ctl->num_block_entries, (unsigned long long)total);
+      if (base + total > ws.e_cap) ws.ctl->overflow = 1u;  // entries beyond the capacity are dropped, never written
+    }
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (lane < kBlocksPerTile) {
+      const unsigned long long off = base + (incl - padded);
       const unsigned long long st = off < ws.e_cap ? off : ws.e_cap;
-      const unsigned long long en = off + s_cnt[b] < ws.e_cap ? off + s_cnt[b] : ws.e_cap;
-      s_start[b] = (unsigned int)st;
-      s_lim[b] = (unsigned int)en;
-      out_jobs[b] = make_uint4((unsigned int)st, (unsigned int)(en - st), (unsigned int)bid * kBlocksPerTile + b, 0u);
-      off += (s_cnt[b] + 1u) & ~1u;
+      const unsigned long long en = off + total_b < ws.e_cap ? off + total_b : ws.e_cap;
+      s_start[lane] = (unsigned int)st;
+      s_lim[lane] = (unsigned int)en;
+      out_jobs[lane] = make_uint4((unsigned int)st, (unsigned int)(en - st), (unsigned int)bid * kBlocksPerTile + lane, 0u);
     }
   }
   __syncthreads();
 
-  // ---- pass 2: place the entries, chunk by chunk ----
+  // ---- pass 2: place the entries; the warp's running position in each block's list lives in registers ----
+  unsigned int pos_b[8];
+#pragma unroll
+  for (int b = 0; b < 8; b++) pos_b[b] = s_start[b] + s_wcnt[warp][b];
+  const unsigned int e_cap = (unsigned int)ws.e_cap;  // a position at or beyond the capacity is dropped (overflow is flagged)
   const unsigned int lt = (1u << lane) - 1u;
-  for (int base = 0; base < n; base += kBlThreads) {
-    const int j = base + tid;
+  for (int c = c_lo; c < c_hi; c++) {
+    const int j = (c << 5) + lane;
     const unsigned int m = j < n ? (unsigned int)ws.pair_mask[range.x + j] : 0u;  // this thread's own store of pass 1
-    unsigned int rank[8];
+    // (Gaussian id, 1-based position in the tile list: what n_contrib records)
+    const uint2 ref = make_uint2(m ? vals[range.x + j] : 0u, (unsigned int)(j + 1));
 #pragma unroll
     for (int b = 0; b < 8; b++) {
       const unsigned int bal = __ballot_sync(0xffffffffu, (m >> b) & 1u);
-      rank[b] = __popc(bal & lt);
-      if (lane == 0) s_wcnt[warp][b] = __popc(bal);
-    }
-    // (Gaussian id, 1-based position in the tile list: what n_contrib records)
-    const uint2 ref = make_uint2(m ? vals[range.x + j] : 0u, (unsigned int)(j + 1));
-    __syncthreads();
-    if (warp < kBlocksPerTile) {  // warp b turns the per-warp counts of block b into exclusive offsets
-      const unsigned int c = lane < kBlWarps ? s_wcnt[lane][warp] : 0u;
-      unsigned int incl = c;
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += t;
+      if ((m >> b) & 1u) {
+        const unsigned int pos = pos_b[b] + __popc(bal & lt);
+        TS_CHECK(pos < s_lim[b] || s_lim[b] == e_cap);
+        if (pos < e_cap) ws.bref[pos] = ref;
       }
-      const unsigned int run = s_run[warp];
-      __syncwarp();
-      if (lane < kBlWarps) s_wcnt[lane][warp] = run + incl - c;
-      if (lane == 31) s_run[warp] = run + incl;
+      pos_b[b] += __popc(bal);
     }
-    __syncthreads();
-    if (m) {
-#pragma unroll
-      for (int b = 0; b < 8; b++) {
-        if ((m >> b) & 1u) {
-          const unsigned int pos = s_start[b] + s_wcnt[warp][b] + rank[b];
-          TS_CHECK(pos < s_lim[b] || s_lim[b] == ws.e_cap);
-          if (pos < s_lim[b]) ws.bref[pos] = ref;
-        }
-      }
-    }
-    __syncthreads();  // s_wcnt is rewritten by the next chunk
   }
 }
 
