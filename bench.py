@@ -483,7 +483,7 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
     import torch
     import torch.distributed as dist
     from transplat_b200.decoder import Gaussians
-    from transplat_b200.parallel import forward_view_sharded
+    from transplat_b200.parallel import NVLS_MIN_WORLD, forward_view_sharded
     from transplat_b200.synthetic import make_scene, upstream_grads
 
     def one_shape(name, hw, per_rank, steps, chunks):
@@ -560,9 +560,10 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
                  "nvls_two_shot_chunked": t_nvls_chunked}
         fastest = min((k for k in named if named[k] is not None), key=lambda k: named[k])
         best = named[fastest]
+        t_default = named["nvls_two_shot" if world >= NVLS_MIN_WORLD and t_nvls is not None else "one_all_reduce"]
         nbytes = n_slab * 4
         return {"shape": name, "views": V, "views_per_rank": per_rank, "gaussians": G, "image": [hw, hw], "steps": steps,
-                "ms_per_step": round(best, 4), "views_per_s": round(V / (best * 1e-3), 1),
+                "ms_per_step": round(t_default, 4), "views_per_s": round(V / (t_default * 1e-3), 1),
                 "ms_per_step_one_all_reduce": round(t_plain, 4),
                 "ms_per_step_chunked_overlap": round(t_overlap, 4) if t_overlap is not None else None, "chunks": chunks,
                 "ms_per_step_fused_multimem": round(t_fused, 4) if t_fused is not None else None,
@@ -570,8 +571,9 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
                 "ms_per_step_nvls_two_shot_chunked": round(t_nvls_chunked, 4) if t_nvls_chunked is not None else None,
                 "nvls_exchange_alone_ms_by_ctas": nvls_alone,
                 "fastest": fastest,
+                "default": "nvls_two_shot" if world >= NVLS_MIN_WORLD else "one_all_reduce",
                 "ms_per_step_without_collective": round(t_local, 4),
-                "exchange_exposed_ms": round(best - t_local, 4),
+                "exchange_exposed_ms": round(t_default - t_local, 4),
                 "all_reduce_exposed_ms": round(t_plain - t_local, 4),
                 "all_reduce_alone_ms": round(t_ar, 4), "all_reduce_bytes": int(nbytes),
                 "all_reduce_bus_gbs": round(2.0 * (world - 1) / world * nbytes / (t_ar * 1e-3) / 1e9, 1),

@@ -31,7 +31,8 @@ loss = ((out.color[0] - target) ** 2).sum() + (out.depth[0] * dLd).sum()
 g_full = torch.autograd.grad(loss, L0)
 # view-sharded: this rank renders views rank, rank+world, ... - every way of summing the gradients, twice each
 # (the symmetric-memory paths cycle two replicas of the slab)
-MODES = {"one_all_reduce": {}, "chunked_overlap": {"overlap_chunks": 3}, "fused_multimem": {"fused_reduce": True},
+MODES = {"default": {}, "one_all_reduce": {"nvls_reduce": False}, "chunked_overlap": {"overlap_chunks": 3, "nvls_reduce": False},
+         "fused_multimem": {"fused_reduce": True},
          "nvls_two_shot": {"nvls_reduce": True}, "nvls_two_shot_chunked": {"nvls_reduce": True, "overlap_chunks": 3}}
 ok = True
 for name, kw in MODES.items():

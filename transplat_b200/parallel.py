@@ -98,6 +98,23 @@ class SymmetricGradSlab:
         return self._side
 
 
+NVLS_MIN_WORLD = int(__import__("os").environ.get("TSPLAT_NVLS_MIN_WORLD", "4"))
+_nvls_state = {"ok": None}
+
+
+def nvls_available() -> bool:
+    """False once setting up the symmetric slab has failed on this process (no multicast support, old driver): the
+    exchange then stays with NCCL.  The first backward tries; rasterize.backward_raw reports the failure here."""
+    return _nvls_state["ok"] is not False
+
+
+def nvls_failed(exc) -> None:
+    if _nvls_state["ok"] is not False:
+        import warnings
+        warnings.warn(f"NVLS gradient exchange unavailable ({exc!r}); using the NCCL all-reduce")
+    _nvls_state["ok"] = False
+
+
 def shard_indices(n: int, rank: int, world: int) -> list:
     """Round-robin ownership: item i belongs to rank i mod world."""
     return list(range(rank, n, world))
@@ -149,13 +166,14 @@ def replicate_with_summed_grads(gaussians: Gaussians, group=None) -> Gaussians:
 
 def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
                          depth_mode: Optional[str] = None, group=None, overlap_chunks: int = 0,
-                         fused_reduce: bool = False, nvls_reduce: bool = False, nvls_ctas: int = 0) -> tuple:
+                         fused_reduce: bool = False, nvls_reduce: Optional[bool] = None, nvls_ctas: int = 0) -> tuple:
     """Each rank renders views rank, rank+N, ... of every scene in the batch.  Returns
     (DecoderOutput for the local views, list of the global view indices rendered here).  Backward
     through the output all-reduces the per-Gaussian gradients once - or, with ``overlap_chunks`` > 1 (one scene per
     call, CUDA decoder), range by range inside the rasterizer's backward, each all-reduce running under the kernels of
     the next Gaussian range (713 MB at C5); with ``fused_reduce`` the
-    per-Gaussian kernel itself reduces them through NVLS multicast memory (SymmetricGradSlab); with ``nvls_reduce`` the
+    per-Gaussian kernel itself reduces them through NVLS multicast memory (SymmetricGradSlab); with ``nvls_reduce`` (default:
+    from 4 ranks up, when the system supports multicast memory) the
     kernels write this rank's replica and csrc/exchange.cu sums the replicas through the switch (``overlap_chunks`` > 1:
     range by range on a side stream, under the per-Gaussian kernel of the next range; ``nvls_ctas``: its grid)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -164,6 +182,10 @@ def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, 
     mine = shard_indices(v, rank, world)
     staged = world > 1 and overlap_chunks > 1 and gaussians.means.shape[0] == 1 and gaussians.means.is_cuda
     fused = world > 1 and fused_reduce and gaussians.means.is_cuda
+    if nvls_reduce is None:
+        # measured on B200 / NVSwitch (profiles/r02_experiments.md): NCCL's peer-to-peer all-reduce wins at 2 GPUs, the
+        # two-shot exchange through the switch at 8 (its traffic per GPU does not grow with the number of GPUs)
+        nvls_reduce = world >= NVLS_MIN_WORLD and overlap_chunks <= 1 and not fused_reduce and nvls_available()
     nvls = world > 1 and nvls_reduce and not fused and gaussians.means.is_cuda
     if nvls:
         staged = False

@@ -311,9 +311,17 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
         reduce = cfg.grad_reduce
         multimem = reduce is not None and reduce[1] == "multimem"
         nvls = reduce is not None and reduce[1] == "nvls"
+        nccl_fallback = False
         if multimem or nvls:
-            from .parallel import SymmetricGradSlab
-            sym = SymmetricGradSlab.get(reduce[0], dev, offs[-1] + _pad64(sizes[-1]))
+            from . import parallel
+            try:
+                sym = parallel.SymmetricGradSlab.get(reduce[0], dev, offs[-1] + _pad64(sizes[-1]))
+            except Exception as exc:  # no multicast support here: every rank of the box fails alike
+                if multimem:
+                    raise
+                parallel.nvls_failed(exc)
+                nvls, nccl_fallback = False, True
+        if multimem or nvls:
             # multimem: this rank's replica, zeroed; every rank has zeroed its own before anyone adds
             slab = sym.begin_step() if multimem else sym.next_replica()
         else:
@@ -362,7 +370,7 @@ def backward_raw(cfg: RenderConfig, state, grad_color, grad_depth, grad_loss=Non
             if g_m2d is not None:
                 raise RuntimeError("grad_reduce='nvls' does not cover the screen-space gradient (level 1 only)")
             _backward_nvls(state, launch, sym, stream, offs, sizes, means, int(reduce[2]), int(reduce[3]))
-        elif reduce is None or means.shape[0] != 1:
+        elif reduce is None or means.shape[0] != 1 or nccl_fallback:
             launch()
             if reduce is not None:  # several scenes per call: their Gaussian ranges are not contiguous in the slab
                 import torch.distributed as dist
