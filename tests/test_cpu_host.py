@@ -63,6 +63,25 @@ def test_layout_rejects_bad_arguments():
     assert L.tsplat_workspace_layout(C.byref(_problem()), 1 << 30, C.byref(lay)) == _lib.TSPLAT_EINVAL
 
 
+def test_nvls_exchange_rejects_bad_arguments():
+    """tsplat_nvls_all_reduce (csrc/exchange.cu) validates before it touches the device: null / unaligned slab, more than
+    four pieces, a rank outside the world, pieces that are not whole 16-byte units.  (Its arithmetic is checked on 2, 4
+    and 8 GPUs by scripts/dist_gpu_check.py against the whole-scene gradients: profiles/*view_sharding_check*.)"""
+    L = _lib.lib()
+    offs, cnts = (C.c_uint64 * 4)(0, 0, 0, 0), (C.c_uint64 * 4)(16, 0, 0, 0)
+    slab = C.c_void_p(0x7f0000000000)  # never dereferenced on the host
+    assert L.tsplat_nvls_all_reduce(None, offs, cnts, 1, 0, 2, 0, None) == _lib.TSPLAT_EINVAL
+    assert L.tsplat_nvls_all_reduce(C.c_void_p(0x7f0000000004), offs, cnts, 1, 0, 2, 0, None) == _lib.TSPLAT_EINVAL
+    assert L.tsplat_nvls_all_reduce(slab, offs, cnts, 5, 0, 2, 0, None) == _lib.TSPLAT_EINVAL
+    assert L.tsplat_nvls_all_reduce(slab, offs, cnts, 1, 2, 2, 0, None) == _lib.TSPLAT_EINVAL
+    assert b"rank outside the world" in L.tsplat_last_error()
+    cnts[0] = 18
+    assert L.tsplat_nvls_all_reduce(slab, offs, cnts, 1, 0, 2, 0, None) == _lib.TSPLAT_EINVAL
+    assert b"16-byte units" in L.tsplat_last_error()
+    cnts[0] = 0
+    assert L.tsplat_nvls_all_reduce(slab, offs, cnts, 1, 0, 2, 0, None) == _lib.TSPLAT_OK  # nothing to do: no launch
+
+
 def test_no_cpu_fallback():
     from transplat_b200.decoder import DecoderSplattingCUDA, Gaussians
     dec = DecoderSplattingCUDA()
