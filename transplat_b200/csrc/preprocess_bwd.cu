@@ -112,13 +112,18 @@ __device__ __forceinline__ int sh_basis_backward(int deg, int sh_l4, float x, fl
   return n;
 }
 
-#ifndef TSPLAT_PREB_WARPS_PER_SM
-#define TSPLAT_PREB_WARPS_PER_SM 16  // register budget: 65536 / (32 x 16) = 128 per thread (24 -> 80 registers with spills, 72.2 us; 16 -> 70.9 us at C2)
+// resident CTAs per SM (the register budget): 4-warp CTAs at C2: 4 / 5 / 6 -> 65.7 / 52.1 / 55.0 us (128 / 102 / 80
+// registers per thread, the last with spills)
+#ifndef TSPLAT_PREB_MIN_BLOCKS4
+#define TSPLAT_PREB_MIN_BLOCKS4 5
+#endif
+#ifndef TSPLAT_PREB_MIN_BLOCKS8
+#define TSPLAT_PREB_MIN_BLOCKS8 3  // 8-warp CTAs (more than 4 views per scene) at C5: 2 / 3 -> 2.38 / 2.01 ms
 #endif
 // NW warps per CTA (4 or 8: at least 4 even for fewer views, so that phase B's 2400 outputs are at most 19 per thread and
 // stay in registers)
 template <int NW, int LAYOUT>
-__global__ void __launch_bounds__(kBwdG * NW, TSPLAT_PREB_WARPS_PER_SM / NW) preprocess_backward_kernel(PreBwdArgs a, Workspace ws) {
+__global__ void __launch_bounds__(kBwdG * NW, NW == 4 ? TSPLAT_PREB_MIN_BLOCKS4 : TSPLAT_PREB_MIN_BLOCKS8) preprocess_backward_kernel(PreBwdArgs a, Workspace ws) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   uint64_t* bar = reinterpret_cast<uint64_t*>(smem_raw);
   float* s_mean = reinterpret_cast<float*>(smem_raw + 16);
