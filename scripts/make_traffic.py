@@ -10,6 +10,7 @@ scale = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 stage_of = {"preprocess_forward_kernel": "preprocess", "bucket_scan_kernel": "bin_emit", "bucket_emit_kernel": "bin_emit",
             "tile_sort_gather_kernel": "sort", "big_tile_sort_gather_kernel": "sort", "block_lists_kernel": "ranges_gather",
             "render_forward_kernel": "render_forward", "render_backward_kernel": "render_backward",
+            "render_backward2_kernel": "render_backward",
             "preprocess_backward_kernel": "preprocess_backward"}
 per_kernel = {}
 for r in data:
