@@ -363,11 +363,12 @@ def run_ours(args):
 def launches_per_step(n_views: int, T: int) -> int:
     """Kernels of libtsplat.so launched per step (the MSE colour loss runs inside the render kernels).
     bucket path (default): pack_cameras, preprocess_forward, bucket_scan, bucket_emit, tile_sort_gather,
-    big_tile_sort_gather, gather_records, render_forward, status_store, render_backward, preprocess_backward = 11
+    big_tile_sort_gather, block_lists, render_forward, status_store, render_backward, preprocess_backward = 11
     (the memset node that clears the per-tile pair counters is not a kernel of the library and is not counted);
-    onesweep path: pack_cameras, preprocess, bin_emit, sort passes, ranges_gather, render fwd/bwd, preprocess bwd."""
+    onesweep path: pack_cameras, preprocess, bin_emit, sort passes, ranges_gather, block_lists, render_forward,
+    status_store, render_backward, preprocess_backward."""
     if os.environ.get("TSPLAT_SORT", "bucket") == "onesweep":
-        return 8 + sort_passes(n_views, T)
+        return 9 + sort_passes(n_views, T)
     return 11
 
 

@@ -285,7 +285,8 @@ int tsplat_status_read(const void* workspace, TsplatStatus* status_host, void* c
  * (src/misc/benchmarker.py:44-145, model_wrapper.py:209).
  * tsplat_profile_read synchronises on the recorded events and fills ms_host[0..8] with the SUM of
  * each stage's durations over the recorded calls and ms_host[9] with the number of calls summed:
- * 0 zero-fill, 1 preprocess, 2 bin_emit, 3 sort, 4 ranges_gather, 5 render_forward,
+ * 0 zero-fill, 1 preprocess, 2 bin_emit, 3 sort, 4 ranges_gather (tile ranges on the onesweep path + the per-block
+ * lists of both paths: block_lists_kernel), 5 render_forward,
  * 6 zero-fill (bwd), 7 render_backward, 8 preprocess_backward.  n must be >= 10. */
 #define TSPLAT_NUM_STAGES 9
 int tsplat_profile_enable(int on);
