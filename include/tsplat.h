@@ -199,6 +199,22 @@ int tsplat_forward(const TsplatProblem* p, void* workspace, uint64_t workspace_b
                    uint64_t d_cap, float* out_color, float* out_depth, int32_t* out_radii,
                    void* cuda_stream);
 
+/* tsplat_forward without a caller-owned workspace and without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arguments and results as tsplat_forward; the workspace is a static
+ * device array of TSPLAT_NOALLOC_WORKSPACE_BYTES that every GPU loading the library holds until the process exits.
+ *   - a problem whose tsplat_workspace_layout(p, d_cap).total_bytes exceeds that size is rejected with TSPLAT_ENOSPC;
+ *   - the call makes no cudaMalloc / cudaFree / allocating library call; the caller's current device must be the one
+ *     that owns the pointers (the array's device address is resolved per device);
+ *   - all calls on a device share the array: calls that overlap on the GPU (other streams, concurrent graph replays)
+ *     race and must be serialised by the caller; the array keeps the previous call's contents and the forward clears
+ *     what must start at zero itself;
+ *   - an overflow of d_cap poisons the outputs (NaN in the first colour value of every view), as in tsplat_forward;
+ *     there is no backward over the static workspace. */
+#define TSPLAT_NOALLOC_WORKSPACE_BYTES (32u << 20)
+int tsplat_forward_noalloc(const TsplatProblem* p, uint64_t d_cap, float* out_color, float* out_depth,
+                           int32_t* out_radii, void* cuda_stream);
+
 /* Replaces _C.rasterize_gaussians_backward.  Must follow tsplat_forward on
  * the same (problem, workspace).  Gradients are summed over the V views of each scene and
  * WRITTEN (not accumulated):

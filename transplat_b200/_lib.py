@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("TSPLAT_LIB_PATH") or os.path.join(_HERE, "lib", "libt
 CSRC = os.path.join(_HERE, "csrc")
 
 TSPLAT_OK, TSPLAT_EINVAL, TSPLAT_ENOSPC, TSPLAT_ECUDA = 0, 1, 2, 3
+NOALLOC_WORKSPACE_BYTES = 32 << 20  # include/tsplat.h: TSPLAT_NOALLOC_WORKSPACE_BYTES
 SH_GM3, SH_G3M = 0, 1
 COV_TRIU6, COV_FULL9 = 0, 1
 FLAG_REZERO_GRAD_ACC = 1
@@ -25,7 +26,7 @@ DEPTH_MODES = {None: 0, "depth": 1, "disparity": 2, "relative_disparity": 3, "lo
 EXPORTS = ("tsplat_version", "tsplat_last_error", "tsplat_workspace_layout", "tsplat_forward",
            "tsplat_backward", "tsplat_mark_visible", "tsplat_pack_cameras", "tsplat_status_read", "tsplat_profile_enable",
            "tsplat_profile_read", "tsplat_adapter_forward", "tsplat_adapter_backward", "tsplat_forward_mse",
-           "tsplat_backward_mse", "tsplat_cov3d_forward", "tsplat_cov3d_backward", "tsplat_nvls_all_reduce")
+           "tsplat_backward_mse", "tsplat_cov3d_forward", "tsplat_cov3d_backward", "tsplat_nvls_all_reduce", "tsplat_forward_noalloc")
 
 
 class TsplatProblem(C.Structure):
@@ -96,6 +97,8 @@ def lib():
                                           C.c_void_p, C.c_void_p, C.POINTER(TsplatMse), C.c_void_p]
         L.tsplat_adapter_forward.argtypes = [C.c_void_p] * 7
         L.tsplat_adapter_backward.argtypes = [C.c_void_p] * 8
+        L.tsplat_forward_noalloc.argtypes = [C.POINTER(TsplatProblem), C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p,
+                                             C.c_void_p]
         L.tsplat_nvls_all_reduce.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32,
                                              C.c_int32, C.c_void_p]
         L.tsplat_cov3d_forward.argtypes = [C.c_int32, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p, C.c_void_p]
