@@ -502,10 +502,12 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
         cam = [t[None].to(dev) for t in (sc.extrinsics, sc.intrinsics, sc.near, sc.far)]
         one = torch.ones((), device=dev)
 
-        def step(reduce=True, overlap=0, fused=False, nvls=False, ctas=0):
+        def step(reduce=True, overlap=0, fused=False, nvls=False, ctas=0, default=False):
             leaves = [stat[k].detach().requires_grad_(True) for k in ("means", "cov", "sh", "op")]
             g = Gaussians(*leaves)
-            if reduce:
+            if default:  # what a caller gets without choosing: parallel.forward_view_sharded picks the exchange
+                out, _ = forward_view_sharded(decoder, g, *cam, (hw, hw), depth_mode="depth")
+            elif reduce:
                 out, _ = forward_view_sharded(decoder, g, *cam, (hw, hw), depth_mode="depth", overlap_chunks=overlap,
                                               fused_reduce=fused, nvls_reduce=nvls, nvls_ctas=ctas)
             else:  # the same local views, no collective: what the step costs without the exchange
@@ -540,12 +542,14 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
         n_slab = _pad64(G * 3) + _pad64(G * 9) + _pad64(G * 75) + _pad64(G)
         # our own exchange kernel through the switch (csrc/exchange.cu): whole slab behind the kernels, and range by
         # range on a side stream under the per-Gaussian kernel of the next range; then alone, over its grid size
-        t_nvls = t_nvls_chunked = None
+        t_nvls = t_nvls_chunked = t_nvls_chunked2 = t_nvls_chunked4 = None
         nvls_alone = {}
         try:
             from transplat_b200.parallel import SymmetricGradSlab
             t_nvls = time_it(lambda: step(True, 0, nvls=True), steps)
             t_nvls_chunked = time_it(lambda: step(True, chunks, nvls=True), steps) if chunks > 1 else None
+            t_nvls_chunked2 = time_it(lambda: step(True, 2 * chunks, nvls=True), steps) if chunks > 1 else None
+            t_nvls_chunked4 = time_it(lambda: step(True, 4 * chunks, nvls=True), steps) if chunks > 1 else None
             sym = SymmetricGradSlab.get(None, dev, n_slab)
 
             def alone(c):
@@ -564,7 +568,7 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
                  "nvls_two_shot_chunked": t_nvls_chunked}
         fastest = min((k for k in named if named[k] is not None), key=lambda k: named[k])
         best = named[fastest]
-        t_default = named["nvls_two_shot" if world >= NVLS_MIN_WORLD and t_nvls is not None else "one_all_reduce"]
+        t_default = time_it(lambda: step(default=True), steps)
         nbytes = n_slab * 4
         return {"shape": name, "views": V, "views_per_rank": per_rank, "gaussians": G, "image": [hw, hw], "steps": steps,
                 "ms_per_step": round(t_default, 4), "views_per_s": round(V / (t_default * 1e-3), 1),
@@ -573,9 +577,12 @@ def run_view_sharded(args, dev, decoder, flush, barrier, world, rank, ms_scene_s
                 "ms_per_step_fused_multimem": round(t_fused, 4) if t_fused is not None else None,
                 "ms_per_step_nvls_two_shot": round(t_nvls, 4) if t_nvls is not None else None,
                 "ms_per_step_nvls_two_shot_chunked": round(t_nvls_chunked, 4) if t_nvls_chunked is not None else None,
+                "ms_per_step_nvls_two_shot_chunked_twice_the_chunks": round(t_nvls_chunked2, 4) if t_nvls_chunked2 is not None else None,
+                "ms_per_step_nvls_two_shot_chunked_four_times_the_chunks": round(t_nvls_chunked4, 4) if t_nvls_chunked4 is not None else None,
                 "nvls_exchange_alone_ms_by_ctas": nvls_alone,
                 "fastest": fastest,
-                "default": "nvls_two_shot" if world >= NVLS_MIN_WORLD else "one_all_reduce",
+                "default": "forward_view_sharded() with no options: ncclAllReduce below %d ranks, from there the NVLS "
+                           "exchange, range by range under the per-Gaussian kernel when the slab is large" % NVLS_MIN_WORLD,
                 "ms_per_step_without_collective": round(t_local, 4),
                 "exchange_exposed_ms": round(t_default - t_local, 4),
                 "all_reduce_exposed_ms": round(t_plain - t_local, 4),

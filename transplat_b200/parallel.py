@@ -94,11 +94,15 @@ class SymmetricGradSlab:
     @property
     def side_stream(self):
         if not hasattr(self, "_side"):
-            self._side = torch.cuda.Stream(device=self.bufs[0].device)
+            # high priority: the exchange's few CTAs must get SM slots as soon as any free up, or the block scheduler
+            # keeps feeding the per-Gaussian kernel's queued CTAs and the two kernels run back to back
+            self._side = torch.cuda.Stream(device=self.bufs[0].device, priority=-1)
         return self._side
 
 
 NVLS_MIN_WORLD = int(__import__("os").environ.get("TSPLAT_NVLS_MIN_WORLD", "4"))
+NVLS_CHUNKS = int(__import__("os").environ.get("TSPLAT_NVLS_CHUNKS", "6"))
+NVLS_CHUNK_MIN_BYTES = 256 << 20
 _nvls_state = {"ok": None}
 
 
@@ -165,7 +169,7 @@ def replicate_with_summed_grads(gaussians: Gaussians, group=None) -> Gaussians:
 
 
 def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
-                         depth_mode: Optional[str] = None, group=None, overlap_chunks: int = 0,
+                         depth_mode: Optional[str] = None, group=None, overlap_chunks: Optional[int] = None,
                          fused_reduce: bool = False, nvls_reduce: Optional[bool] = None, nvls_ctas: int = 0) -> tuple:
     """Each rank renders views rank, rank+N, ... of every scene in the batch.  Returns
     (DecoderOutput for the local views, list of the global view indices rendered here).  Backward
@@ -180,12 +184,20 @@ def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, 
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     v = extrinsics.shape[1]
     mine = shard_indices(v, rank, world)
+    auto_chunks = overlap_chunks is None
+    overlap_chunks = 0 if auto_chunks else int(overlap_chunks)
     staged = world > 1 and overlap_chunks > 1 and gaussians.means.shape[0] == 1 and gaussians.means.is_cuda
     fused = world > 1 and fused_reduce and gaussians.means.is_cuda
     if nvls_reduce is None:
         # measured on B200 / NVSwitch (profiles/r02_experiments.md): NCCL's peer-to-peer all-reduce wins at 2 GPUs, the
         # two-shot exchange through the switch at 8 (its traffic per GPU does not grow with the number of GPUs)
-        nvls_reduce = world >= NVLS_MIN_WORLD and overlap_chunks <= 1 and not fused_reduce and nvls_available()
+        nvls_reduce = world >= NVLS_MIN_WORLD and (auto_chunks or overlap_chunks <= 1) and not fused_reduce and \
+            nvls_available()
+    if auto_chunks and nvls_reduce and gaussians.means.shape[0] == 1 and \
+            gaussians.means.shape[1] * 88 * 4 >= NVLS_CHUNK_MIN_BYTES:
+        # a large slab (C5: 738 MB) is exchanged range by range under the per-Gaussian kernel of the next range; for
+        # a small one (C2: 46 MB) the extra launches cost more than the overlap hides (measured)
+        overlap_chunks = NVLS_CHUNKS
     nvls = world > 1 and nvls_reduce and not fused and gaussians.means.is_cuda
     if nvls:
         staged = False

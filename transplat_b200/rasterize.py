@@ -421,6 +421,7 @@ def _backward_nvls(state, launch, sym, stream, offs, sizes, means, chunks, num_c
         return
     per = -(-G // chunks)
     step = -(-per // 64) * 64  # ranges start at multiples of 64 (the per-Gaussian kernel's CTA; 16-byte units too)
+    num_ctas = num_ctas or 16  # link-bound from 16 CTAs up (measured): leave the SMs to the kernel it runs under
     per_g = [n // G for n in sizes]  # floats per Gaussian in each of the four pieces
     side = sym.side_stream
     base_flags = state.problem.flags
