@@ -42,6 +42,16 @@ def case(name: str):
         sc.means[:, 2] = 4.0
         sc.extrinsics[:] = torch.eye(4)
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=30.0, bg=(0.0, 0.0, 0.0))
+    if name == "many_views_l2":    # 11 views of a scene in one call: more views than the per-Gaussian kernels have warps
+        # (8 per CTA), so preprocess forward AND backward take their second round with 3 live warps
+        sc = make_scene(n_ctx=1, h=36, w=36, n_views=11, render_hw=(48, 40), seed=61)
+        return _pack(sc, level=2, B=2, depth_mode=1, cov_mul=3.0, bg=(0.2, 0.0, 0.4), drop=3)
+    if name == "many_views_l1":    # the same with the level-1 layouts ([G, M, 3] harmonics, [G, 6] covariances), 9 views
+        sc = make_scene(n_ctx=1, h=32, w=32, n_views=9, render_hw=(40, 56), seed=62, sh_degree=3)
+        return _pack(sc, level=1, B=1, depth_mode=0, cov_mul=3.0, bg=(0.0, 0.3, 0.1))
+    if name == "sub_tile":         # an image smaller than one 16x16 tile (9 x 7 pixels): one partial tile, partial blocks
+        sc = make_scene(n_ctx=1, h=12, w=12, n_views=2, render_hw=(7, 9), seed=63)
+        return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=0.5, bg=(0.5, 0.5, 0.5))
     if name == "c2":               # BASELINE config 2: 131072 Gaussians, 4 views, 256x256, colour+depth
         sc = make_scene()
         return _pack(sc, level=2, B=1, depth_mode=1, cov_mul=1.0, bg=(0.0, 0.0, 0.0))

@@ -41,7 +41,8 @@ def _assert_reports(fwd, bwd):
 
 
 @pytest.mark.parametrize("sort", ["bucket", "onesweep"])
-@pytest.mark.parametrize("name", ["tiny_l1", "deg2_l1", "small_l2_depth", "ragged_l2", "mid_l2", "coplanar"])
+@pytest.mark.parametrize("name", ["tiny_l1", "deg2_l1", "small_l2_depth", "ragged_l2", "mid_l2", "coplanar",
+                                  "many_views_l2", "many_views_l1", "sub_tile"])
 def test_stage_by_stage_parity(name, sort):
     """Both binning paths (per-tile bucket sort; global onesweep LSD radix sort) against the oracle."""
     *args, cfg = case(name)
