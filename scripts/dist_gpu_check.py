@@ -1,5 +1,7 @@
-"""torchrun --nproc-per-node N scripts/dist_gpu_check.py: view sharding over N GPUs (NCCL all-reduce of the flat
-per-Gaussian gradient slab, transplat_b200/parallel.py) against the same scene rendered whole on each rank."""
+"""torchrun --nproc-per-node N scripts/dist_gpu_check.py: view sharding over N GPUs against the same scene rendered whole
+on each rank, for every way of summing the per-Gaussian gradients (transplat_b200/parallel.py): the default choice, one
+NCCL all-reduce, chunked NCCL, multimem.red fused into the producing kernel, the library's two-shot NVLS exchange whole
+and range by range.  Each twice in a row (the symmetric-memory paths cycle two replicas)."""
 import os, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
