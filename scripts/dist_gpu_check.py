@@ -58,6 +58,33 @@ for name, kw in MODES.items():
         if rank == 0:
             print(f"view sharding over {world} GPUs [{name} #{rep}]: views/rank {len(mine)}, max rel gradient error vs "
                   f"whole-scene {t[0]:.3e}, image error {t[1]:.3e}", "OK" if good else "FAIL")
+# the default step captured in a CUDA graph (exchange kernels and barriers included) and replayed three times: the
+# gradients each replay leaves behind against the whole-scene gradients
+try:
+    from transplat_b200.graphs import GraphedStep
+    L2 = leaves()
+    idx2 = torch.arange(rank, V, world, device=dev)
+
+    def graphed_step():
+        o, _ = forward_view_sharded(dec, Gaussians(*L2), *cam, (HW, HW), depth_mode="depth")
+        l = ((o.color[0] - target[idx2]) ** 2).sum() + (o.depth[0] * dLd[idx2]).sum()
+        return torch.autograd.grad(l, L2)
+    gs = GraphedStep(graphed_step)
+    for rep in range(3):
+        g_shard = gs.replay()
+        torch.cuda.synchronize()
+        err = max(float((a - b).abs().max() / a.abs().max()) for a, b in zip(g_full, g_shard))
+        t = torch.tensor([err], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        good = bool(t[0] < 1e-4)
+        ok = ok and good
+        if rank == 0:
+            print(f"view sharding over {world} GPUs [default, CUDA-graph replay #{rep}]: max rel gradient error vs whole-scene "
+                  f"{t[0]:.3e}", "OK" if good else "FAIL")
+except Exception as exc:
+    ok = False
+    if rank == 0:
+        print(f"graphed default step: FAILED ({exc!r})")
 if rank == 0:
     print("ALL OK" if ok else "SOME FAILED")
 dist.destroy_process_group()

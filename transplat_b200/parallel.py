@@ -206,7 +206,7 @@ def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, 
     if not mine:
         # a rank without views would skip backward and leave the others waiting in the all-reduce
         raise ValueError(f"view sharding needs at least one view per rank (views={v}, ranks={world})")
-    idx = torch.tensor(mine, device=extrinsics.device)
+    idx = torch.arange(rank, v, world, device=extrinsics.device)  # = mine; built on the device (capturable in a CUDA graph)
     if nvls:
         extra = {"grad_reduce": (group, "nvls", int(overlap_chunks), int(nvls_ctas))}
     elif fused:
