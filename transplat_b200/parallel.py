@@ -19,6 +19,7 @@
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Sequence
 
 import torch
@@ -100,9 +101,11 @@ class SymmetricGradSlab:
         return self._side
 
 
-NVLS_MIN_WORLD = int(__import__("os").environ.get("TSPLAT_NVLS_MIN_WORLD", "4"))
-NVLS_CHUNKS = int(__import__("os").environ.get("TSPLAT_NVLS_CHUNKS", "6"))
-NVLS_CHUNK_MIN_BYTES = 256 << 20
+# Exchange policy of forward_view_sharded() when the caller does not choose (measured on 2 / 4 / 8 B200 of one NVSwitch
+# domain, profiles/r02_experiments.md)
+NVLS_MIN_WORLD = int(os.environ.get("TSPLAT_NVLS_MIN_WORLD", "4"))   # ranks from which the NVLS exchange beats ncclAllReduce
+NVLS_CHUNKS = int(os.environ.get("TSPLAT_NVLS_CHUNKS", "6"))         # Gaussian ranges a large slab is exchanged in
+NVLS_CHUNK_MIN_BYTES = 256 << 20                                     # "large": below it the slab goes whole
 _nvls_state = {"ok": None}
 
 
