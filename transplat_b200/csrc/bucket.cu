@@ -248,7 +248,17 @@ __device__ __forceinline__ void write_sorted_tile(const Workspace& ws, const uns
 constexpr int kTileSortThreads = 512;
 constexpr int kTileSortWarps = kTileSortThreads / 32;
 
-constexpr int kDepthBuckets = 4096;  // depth buckets of the distribution sort (>= kSmallTileCap keeps ~1 word/bucket)
+// 2048 depth buckets (74 KB of shared memory per CTA) and 40 registers let THREE 512-thread CTAs share an SM: the kernel
+// is bound by shared-memory latency and barriers, not by issue.  C2: 4096 buckets x 2 CTAs 34.8 us, 2048 x 2 33.3,
+// 2048 x 3 29.4.
+#ifndef TSPLAT_DEPTH_BUCKET_BITS
+#define TSPLAT_DEPTH_BUCKET_BITS 11
+#endif
+#ifndef TSPLAT_TS_MIN_BLOCKS
+#define TSPLAT_TS_MIN_BLOCKS 3
+#endif
+constexpr int kDepthBucketBits = TSPLAT_DEPTH_BUCKET_BITS;
+constexpr int kDepthBuckets = 1 << kDepthBucketBits;  // depth buckets of the distribution sort (at most 2 words per bucket on average)
 constexpr int kMaxBucketFill = 48;   // a fuller bucket (clustered or equal depths) sends the tile to the radix path
 
 struct TileSortSmem {
@@ -285,7 +295,7 @@ __device__ __forceinline__ bool distribution_sort_tile(TileSortSmem& s, int n, i
   __syncthreads();
   const unsigned int dmin = s.dmin, range = s.dmax - dmin;
   const int bits = 32 - __clz(range);  // 0 when every depth is equal
-  const int shift = max(0, bits - 12);
+  const int shift = max(0, bits - kDepthBucketBits);
   unsigned short rank[KMAX];
 #pragma unroll
   for (int k = 0; k < KMAX; k++) {
@@ -417,7 +427,7 @@ __device__ __forceinline__ void radix_sort_tile_by_depth(TileSortSmem& s, int n,
   }
 }
 
-__global__ void __launch_bounds__(kTileSortThreads, 2) tile_sort_gather_kernel(Workspace ws, int G,
+__global__ void __launch_bounds__(kTileSortThreads, TSPLAT_TS_MIN_BLOCKS) tile_sort_gather_kernel(Workspace ws, int G,
                                                                             const unsigned long long* __restrict__ pairs,
                                                                             unsigned long long* __restrict__ keys_out,
                                                                             unsigned int* __restrict__ vals_out) {
