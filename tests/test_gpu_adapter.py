@@ -99,7 +99,7 @@ def test_adapter_feeds_the_rasterizer_unchanged():
     dec = DecoderSplattingCUDA().cuda()
     out = dec.forward(flat, ext.cuda(), intr.cuda(), torch.ones(b, v).cuda(), torch.full((b, v), 100.0).cuda(), (h, w),
                       depth_mode="depth")
-    assert float(out.color.mean()) > 0.01 and float(out.depth.max()) > 1.0
+    assert float(out.color.detach().mean()) > 0.01 and float(out.depth.detach().max()) > 1.0
     (out.color.sum() + out.depth.sum()).backward()
     assert float(raw.grad.abs().max()) > 0 and float(depths.grad.abs().max()) > 0
     assert torch.isfinite(raw.grad).all() and torch.isfinite(depths.grad).all()
