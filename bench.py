@@ -419,14 +419,23 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
     lay_in = SlabLayout(dict(means=(1, G, 3), cov=(1, G, 3, 3), sh=(1, G, 3, 25), op=(1, G), ext=(1, VIEWS, 4, 4),
                              intr=(1, VIEWS, 3, 3), near=(1, VIEWS), far=(1, VIEWS), target=(1, VIEWS, 3, HW, HW),
                              dLd=(1, VIEWS, HW, HW)))
-    host = [dict(slab=lay_in.pack_pinned(dict(
-        means=s.means[None], cov=s.covariances[None], sh=s.harmonics[None], op=s.opacities[None], ext=s.extrinsics[None],
-        intr=s.intrinsics[None], near=s.near[None], far=s.far[None], target=target_h[None], dLd=dLd_h[None])))
-        for s in scenes]
     lay_img = SlabLayout(dict(color=(1, VIEWS, 3, HW, HW), depth=(1, VIEWS, HW, HW)))
     lay_grad = SlabLayout(dict(g_means=(1, G, 3), g_cov=(1, G, 3, 3), g_sh=(1, G, 3, 25), g_op=(1, G)))
     n_out = 4  # result buffers cycled (a consumer would read them between steps)
-    outs = [dict(images=lay_img.empty_pinned(), grads=lay_grad.empty_pinned()) for _ in range(n_out)]
+    # the staging buffers are allocated with this rank bound to its GPU's NUMA node (TSPLAT_NUMA=0: wherever it runs)
+    from transplat_b200.streaming import numa_local
+    import contextlib
+    numa = numa_local(dev) if os.environ.get("TSPLAT_NUMA", "1") != "0" else contextlib.nullcontext()
+    with numa:
+        host = [dict(slab=lay_in.pack_pinned(dict(
+            means=s.means[None], cov=s.covariances[None], sh=s.harmonics[None], op=s.opacities[None], ext=s.extrinsics[None],
+            intr=s.intrinsics[None], near=s.near[None], far=s.far[None], target=target_h[None], dLd=dLd_h[None])))
+            for s in scenes]
+        outs = [dict(images=lay_img.empty_pinned(), grads=lay_grad.empty_pinned()) for _ in range(n_out)]
+        for o in outs:  # first touch while bound
+            for t in o.values():
+                t.zero_()
+    numa_info = getattr(numa, "info", {"bound": False, "disabled": True})
     one = torch.ones((), device=dev)
     h2d = host[0]["slab"].numel() * 4
     d2h = sum(t.numel() * 4 for t in outs[0].values())
@@ -479,7 +488,8 @@ def run_e2e(args, dev, decoder, scenes, target_h, dLd_h, flush, barrier, world):
             "how": "pinned host slab (Gaussians, cameras, target) -> H2D stream -> kernels -> D2H stream -> pinned host "
                    "slabs (colour+depth, all four gradients), 3 slots in flight"
                    + ("" if args.eager else ", the kernels of a step replayed from one CUDA graph per slot") + "; "
-                   f"{N_SCENES} scenes x {h2d >> 20} MiB cycled (> L2), window timed with CUDA events"}
+                   f"{N_SCENES} scenes x {h2d >> 20} MiB cycled (> L2), window timed with CUDA events",
+            "numa": numa_info}
 
 
 # ------------------------------------------------------------------------------------------------

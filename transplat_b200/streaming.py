@@ -50,6 +50,58 @@ class SlabLayout:
         return torch.empty(self.total, dtype=torch.float32).pin_memory()
 
 
+def _parse_cpulist(text: str) -> set:
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        lo, _, hi = part.partition("-")
+        cpus.update(range(int(lo), int(hi or lo) + 1))
+    return cpus
+
+
+class numa_local:
+    """``with numa_local(device): allocate pinned buffers`` - runs the block with this thread bound to the CPUs of the
+    NUMA node the GPU hangs off, so that the pinned host memory it allocates is local to that GPU's PCIe root (first
+    touch), then restores the affinity.  With one rank per GPU on a two-socket host, unbound ranks put half of their
+    staging buffers behind the socket interconnect.  Best effort: without /sys, on a single node or inside a cpuset
+    that excludes the node it does nothing; ``info`` says what happened."""
+
+    def __init__(self, device):
+        self.device = torch.device(device)
+        self.info = {"bound": False}
+        self._saved = None
+
+    def __enter__(self):
+        import os
+        try:
+            props = torch.cuda.get_device_properties(self.device)
+            bus = "%04x:%02x:%02x.0" % (getattr(props, "pci_domain_id", 0), props.pci_bus_id, props.pci_device_id)
+            node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+            self.info.update(pci=bus, numa_node=node)
+            if node >= 0:
+                cpus = _parse_cpulist(open(f"/sys/devices/system/node/node{node}/cpulist").read())
+                have = os.sched_getaffinity(0)
+                want = cpus & have
+                self.info.update(node_cpus=len(cpus), usable_cpus=len(want))
+                if want and want != have:
+                    self._saved = have
+                    os.sched_setaffinity(0, want)
+                    self.info["bound"] = True
+        except Exception as exc:  # no sysfs, no such attribute, no permission: stay as we are
+            self.info["error"] = repr(exc)
+        return self
+
+    def __exit__(self, *exc):
+        import os
+        if self._saved is not None:
+            try:
+                os.sched_setaffinity(0, self._saved)
+            except Exception:
+                pass
+        return False
+
+
 class HostPipeline:
     def __init__(self, device: torch.device, slots: int = 3, trace: bool = False):
         self.device = device
