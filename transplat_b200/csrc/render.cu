@@ -902,14 +902,17 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_BWD2_MIN_BLOCKS) render
               C0 += vw.y * dl.x; C1 += vw.y * dl.y; C2 += vw.y * dl.z;
               if (CH == 4) C3 += vw.y * dl.w;
             }
-            if (kBwdParts == 2) {
+            if (kBwdParts > 1) {  // join the parts of an entry: lanes row, row + kBwdRows, ...
               const unsigned int full = 0xffffffffu;
-              Sx += __shfl_xor_sync(full, Sx, 16); Sy += __shfl_xor_sync(full, Sy, 16);
-              Sxx += __shfl_xor_sync(full, Sxx, 16); Sxy += __shfl_xor_sync(full, Sxy, 16);
-              Syy += __shfl_xor_sync(full, Syy, 16); Sop += __shfl_xor_sync(full, Sop, 16);
-              C0 += __shfl_xor_sync(full, C0, 16); C1 += __shfl_xor_sync(full, C1, 16);
-              C2 += __shfl_xor_sync(full, C2, 16);
-              if (CH == 4) C3 += __shfl_xor_sync(full, C3, 16);
+#pragma unroll
+              for (int off = kBwdRows; off < 32; off <<= 1) {
+                Sx += __shfl_xor_sync(full, Sx, off); Sy += __shfl_xor_sync(full, Sy, off);
+                Sxx += __shfl_xor_sync(full, Sxx, off); Sxy += __shfl_xor_sync(full, Sxy, off);
+                Syy += __shfl_xor_sync(full, Syy, off); Sop += __shfl_xor_sync(full, Sop, off);
+                C0 += __shfl_xor_sync(full, C0, off); C1 += __shfl_xor_sync(full, C1, off);
+                C2 += __shfl_xor_sync(full, C2, off);
+                if (CH == 4) C3 += __shfl_xor_sync(full, C3, off);
+              }
             }
             if (part == 0 && ((rowmask >> row) & 1u)) {
               TS_CHECK(gid < (unsigned int)G);
