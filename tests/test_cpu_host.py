@@ -193,3 +193,18 @@ def test_unmodified_reference_file_marshals_like_the_batched_path(monkeypatch):
         assert torch.equal(c["cov"][0], (t("cov") * s ** 2)[:, row, col])
         assert torch.equal(c["feat"][0], t("harmonics").permute(0, 2, 1))   # [G, M, 3]
         assert torch.equal(c["opacity"][0], t("opacities"))
+
+
+def test_numa_local_is_best_effort():
+    """streaming.numa_local: the cpulist parser, and that the context manager never raises and restores the affinity
+    (here there is no GPU: it must record the error and bind nothing)."""
+    import os
+
+    from transplat_b200.streaming import _parse_cpulist, numa_local
+    assert _parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}
+    assert _parse_cpulist("") == set()
+    before = os.sched_getaffinity(0)
+    with numa_local("cuda:0") as n:
+        inside = os.sched_getaffinity(0)
+    assert os.sched_getaffinity(0) == before
+    assert n.info["bound"] is False or inside <= before
