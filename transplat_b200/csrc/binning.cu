@@ -333,7 +333,6 @@ __global__ void __launch_bounds__(256) ranges_gather_kernel(Workspace ws, int G)
   const unsigned long long Dfull = ws.ctl->num_rendered;
   const unsigned int D = (unsigned int)(Dfull < ws.d_cap ? Dfull : ws.d_cap);
   const unsigned long long* __restrict__ keys = ws.keys[ws.sort_passes & 1];
-  const unsigned int* __restrict__ vals = ws.vals[ws.sort_passes & 1];
   for (unsigned int j = blockIdx.x * blockDim.x + threadIdx.x; j < D; j += gridDim.x * blockDim.x) {
     const unsigned int tile = (unsigned int)(keys[j] >> 32);
     if (j == 0) ws.ranges[tile].x = 0;
