@@ -208,3 +208,52 @@ def test_numa_local_is_best_effort():
         inside = os.sched_getaffinity(0)
     assert os.sched_getaffinity(0) == before
     assert n.info["bound"] is False or inside <= before
+
+
+def test_capacity_bookkeeping_reads_every_status_block():
+    """rasterize._Capacity with fake events and host blocks (no GPU): every in-flight status block is read exactly once,
+    an overflowed earlier call raises at the sweep AND has already raised the capacity, a block the caller read itself
+    is forgotten, capacities never shrink."""
+    import numpy as np
+
+    from transplat_b200.rasterize import OverflowError_, TsplatStatus, _Capacity
+
+    class FakeEvent:
+        def __init__(self, done):
+            self.done, self.synced = done, 0
+
+        def query(self):
+            return self.done
+
+        def synchronize(self):
+            self.synced += 1
+            self.done = True
+
+    class FakeHost:
+        def __init__(self, d, e, overflow):
+            st = TsplatStatus(num_rendered=d, overflow=overflow, reserved=0, num_block_entries=e, reserved1=0)
+            self.buf = np.frombuffer(bytes(st), dtype=np.uint8).copy()
+
+        def numpy(self):
+            return self.buf
+
+    cap = _Capacity()
+    key = (0, 4, 1000, 64, 64)
+    assert cap.get(key, 4000) >= 4096
+    first = cap.cap[key]
+    ev_done, ev_pending, ev_mine = FakeEvent(True), FakeEvent(False), FakeEvent(False)
+    cap.inflight = [(key, FakeHost(10_000, 21_000, 0), ev_done, first, True),
+                    (key, FakeHost(50_000, 100_000, 1), ev_pending, first, True),
+                    (key, FakeHost(1, 1, 0), ev_mine, first, True)]
+    cap.forget(ev_mine)                       # the caller read that one itself
+    cap.sweep()                               # only the finished one is read; nothing raises
+    assert len(cap.inflight) == 1 and cap.last_num_rendered == 10_000
+    assert cap.cap[key] >= max(2 * 10_000, 21_000 + 1)
+    grown = cap.cap[key]
+    with pytest.raises(OverflowError_):
+        cap.sweep(wait=True)                  # the overflowed call surfaces, once
+    assert cap.inflight == [] and ev_pending.synced == 1
+    assert cap.cap[key] >= max(2 * 50_000, 100_000 + 1) > grown   # and the capacity is already raised
+    cap.observe(key, 10, 10)
+    assert cap.cap[key] >= 100_000            # never shrinks
+    cap.sweep(wait=True)                      # nothing left: no second raise
