@@ -257,3 +257,26 @@ def test_capacity_bookkeeping_reads_every_status_block():
     cap.observe(key, 10, 10)
     assert cap.cap[key] >= 100_000            # never shrinks
     cap.sweep(wait=True)                      # nothing left: no second raise
+
+
+def test_view_sharding_exchange_policy():
+    """parallel.choose_exchange: what forward_view_sharded does when the caller does not choose, and that explicit
+    choices are honoured (no GPU, no process group)."""
+    from transplat_b200.parallel import NVLS_CHUNKS, NVLS_MIN_WORLD, choose_exchange as ce
+    C2, C5 = 131072, 2097152
+    assert ce(1, 1, C2, True, None, False, None, True) == ("none", 0)
+    # defaults: NCCL below NVLS_MIN_WORLD ranks, the NVLS exchange from there; large slabs range by range
+    assert ce(2, 1, C5, True, None, False, None, True) == ("all_reduce", 0)
+    assert ce(NVLS_MIN_WORLD, 1, C2, True, None, False, None, True) == ("nvls", 0)
+    assert ce(8, 1, C5, True, None, False, None, True) == ("nvls", NVLS_CHUNKS)
+    assert ce(8, 2, C5, True, None, False, None, True) == ("nvls", 0)            # several scenes per call: whole slab
+    assert ce(8, 1, C5, True, None, False, None, False) == ("all_reduce", 0)      # no multicast memory on this system
+    assert ce(8, 1, C5, False, None, False, None, True) == ("all_reduce", 0)      # CPU tensors (the gloo tests)
+    # explicit choices
+    assert ce(8, 1, C5, True, 0, False, False, True) == ("all_reduce", 0)
+    assert ce(8, 1, C5, True, 3, False, False, True) == ("staged_all_reduce", 3)
+    assert ce(8, 1, C5, True, 3, False, None, True) == ("staged_all_reduce", 3)   # chunks given, exchange not: NCCL, as before
+    assert ce(2, 1, C2, True, 0, False, True, True) == ("nvls", 0)
+    assert ce(2, 1, C2, True, 4, False, True, True) == ("nvls", 4)
+    assert ce(8, 1, C2, True, None, True, None, True) == ("multimem", 0)
+    assert ce(8, 2, C2, True, 3, False, False, True) == ("all_reduce", 0)         # staging needs one scene per call

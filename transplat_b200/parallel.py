@@ -171,6 +171,35 @@ def replicate_with_summed_grads(gaussians: Gaussians, group=None) -> Gaussians:
     return Gaussians(m, c, h, o)
 
 
+def choose_exchange(world: int, scenes: int, gaussians_per_scene: int, on_cuda: bool, overlap_chunks: Optional[int],
+                    fused_reduce: bool, nvls_reduce: Optional[bool], nvls_ok: bool) -> tuple:
+    """How a view-sharded backward sums its per-Gaussian gradients: returns (mode, chunks) with mode one of
+    "none" (one rank), "all_reduce" (one NCCL all-reduce of the flat slab), "staged_all_reduce" (per Gaussian range, under
+    the next range's kernels), "nvls" (csrc/exchange.cu; chunks > 1: range by range on a side stream), "multimem" (the
+    producing kernel adds with multimem.red).  ``overlap_chunks`` / ``nvls_reduce`` None = decide here, from what was
+    measured on 2 / 4 / 8 B200 of one NVSwitch domain (profiles/r02_experiments.md): NCCL's peer-to-peer all-reduce wins
+    at 2 GPUs, the two-shot exchange through the switch from 4 (its traffic per GPU does not grow with the number of
+    GPUs); a large slab (C5: 738 MB) is exchanged range by range under the per-Gaussian kernel of the next range, for a
+    small one (C2: 46 MB) the extra launches cost more than the overlap hides."""
+    if world <= 1:
+        return "none", 0
+    auto_chunks = overlap_chunks is None
+    chunks = 0 if auto_chunks else int(overlap_chunks)
+    staged = chunks > 1 and scenes == 1 and on_cuda
+    fused = bool(fused_reduce) and on_cuda
+    if nvls_reduce is None:
+        nvls_reduce = world >= NVLS_MIN_WORLD and (auto_chunks or chunks <= 1) and not fused_reduce and nvls_ok
+    if auto_chunks and nvls_reduce and scenes == 1 and gaussians_per_scene * 88 * 4 >= NVLS_CHUNK_MIN_BYTES:
+        chunks = NVLS_CHUNKS
+    if nvls_reduce and not fused and on_cuda:
+        return "nvls", chunks
+    if fused:
+        return "multimem", 0
+    if staged:
+        return "staged_all_reduce", chunks
+    return "all_reduce", 0
+
+
 def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, near, far, image_shape,
                          depth_mode: Optional[str] = None, group=None, overlap_chunks: Optional[int] = None,
                          fused_reduce: bool = False, nvls_reduce: Optional[bool] = None, nvls_ctas: int = 0) -> tuple:
@@ -187,24 +216,11 @@ def forward_view_sharded(decoder, gaussians: Gaussians, extrinsics, intrinsics, 
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     v = extrinsics.shape[1]
     mine = shard_indices(v, rank, world)
-    auto_chunks = overlap_chunks is None
-    overlap_chunks = 0 if auto_chunks else int(overlap_chunks)
-    staged = world > 1 and overlap_chunks > 1 and gaussians.means.shape[0] == 1 and gaussians.means.is_cuda
-    fused = world > 1 and fused_reduce and gaussians.means.is_cuda
-    if nvls_reduce is None:
-        # measured on B200 / NVSwitch (profiles/r02_experiments.md): NCCL's peer-to-peer all-reduce wins at 2 GPUs, the
-        # two-shot exchange through the switch at 8 (its traffic per GPU does not grow with the number of GPUs)
-        nvls_reduce = world >= NVLS_MIN_WORLD and (auto_chunks or overlap_chunks <= 1) and not fused_reduce and \
-            nvls_available()
-    if auto_chunks and nvls_reduce and gaussians.means.shape[0] == 1 and \
-            gaussians.means.shape[1] * 88 * 4 >= NVLS_CHUNK_MIN_BYTES:
-        # a large slab (C5: 738 MB) is exchanged range by range under the per-Gaussian kernel of the next range; for
-        # a small one (C2: 46 MB) the extra launches cost more than the overlap hides (measured)
-        overlap_chunks = NVLS_CHUNKS
-    nvls = world > 1 and nvls_reduce and not fused and gaussians.means.is_cuda
-    if nvls:
-        staged = False
-    if world > 1 and not staged and not fused and not nvls:
+    mode, overlap_chunks = choose_exchange(world, gaussians.means.shape[0], gaussians.means.shape[1],
+                                           gaussians.means.is_cuda, overlap_chunks, fused_reduce, nvls_reduce,
+                                           nvls_available())
+    nvls, fused, staged = mode == "nvls", mode == "multimem", mode == "staged_all_reduce"
+    if mode == "all_reduce":
         gaussians = replicate_with_summed_grads(gaussians, group)
     if not mine:
         # a rank without views would skip backward and leave the others waiting in the all-reduce
