@@ -498,7 +498,9 @@ __global__ void __launch_bounds__(kRenderThreads, TSPLAT_FWD_MIN_BLOCKS) render_
   }
 #ifdef TSPLAT_TIMELINE
   if (lane == 0 && gw < 8192) {
-    g_timeline[gw * 4 + 0] = t_start; g_timeline[gw * 4 + 1] = gtime(); g_timeline[gw * 4 + 2] = n_jobs; g_timeline[gw * 4 + 3] = n_refs;
+    g_timeline[gw * 4 + 0] = t_start; g_timeline[gw * 4 + 1] = gtime(); unsigned int smid;
+    asm("mov.u32 %0, %%smid;" : "=r"(smid));
+    g_timeline[gw * 4 + 2] = n_jobs | ((unsigned long long)smid << 32); g_timeline[gw * 4 + 3] = n_refs;
   }
 #endif
 }
